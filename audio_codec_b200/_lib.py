@@ -1,0 +1,113 @@
+"""ctypes binding of libpac_b200.so (include/pac_b200.h).
+
+There is NO CPU fallback: importing this module without the built library, or
+calling an op without a CUDA device, raises.
+"""
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_PKG = Path(__file__).resolve().parent
+_LIB_PATH = _PKG / "libpac_b200.so"
+
+F32, F64 = 0, 1
+W_SINE, W_START, W_STOP, W_STARTSTOP, W_KAISER, W_NONE = range(6)
+
+
+class PacConfig(C.Structure):
+    _fields_ = [("sample_rate", C.c_int), ("n_channels", C.c_int), ("n_mdct_lines", C.c_int),
+                ("n_scale_bits", C.c_int), ("n_mant_size_bits", C.c_int), ("use_sbr", C.c_int),
+                ("use_vq", C.c_int), ("target_bits_per_sample", C.c_double)]
+
+
+class PacError(RuntimeError):
+    pass
+
+
+def _load():
+    if not _LIB_PATH.exists():
+        raise ImportError(
+            f"{_LIB_PATH} is missing: build it with `python -m audio_codec_b200.build` "
+            "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(str(_LIB_PATH))
+    vp, ll, i, d = C.c_void_p, C.c_longlong, C.c_int, C.c_double
+    sig = {
+        "pac_create": (i, [i, C.POINTER(PacConfig), C.POINTER(vp)]),
+        "pac_destroy": (None, [vp]),
+        "pac_strerror": (C.c_char_p, [i]),
+        "pac_get_bands": (i, [vp, i, C.POINTER(i), C.POINTER(i)]),
+        "pac_mdct_forward": (i, [vp, i, vp, ll, i, i, i, i, vp, vp]),
+        "pac_imdct_ola": (i, [vp, i, vp, i, i, i, i, vp, ll, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola"]
+
+
+def check(rc):
+    if rc < 0:
+        raise PacError(f"libpac_b200: {lib.pac_strerror(rc).decode()} ({rc})")
+    return rc
+
+
+class Context:
+    """One per (GPU, configuration).  Mirrors the reference's CodingParams fields
+    (coder/pacfile.py:157-174, :699-707)."""
+
+    def __init__(self, sample_rate=48000, n_channels=2, rate_kbps=128.0, use_vq=True, use_sbr=None,
+                 n_scale_bits=4, n_mant_size_bits=12, device=None):
+        import torch
+        if not torch.cuda.is_available():
+            raise PacError("no CUDA device: audio_codec_b200 has no CPU path")
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        if use_sbr is None:
+            use_sbr = rate_kbps < 128
+        self.cfg = PacConfig(int(sample_rate), int(n_channels), 1024, int(n_scale_bits), int(n_mant_size_bits),
+                             int(bool(use_sbr)), int(bool(use_vq)), float(rate_kbps) / (sample_rate / 1000))
+        self.rate_kbps = rate_kbps
+        h = C.c_void_p()
+        check(lib.pac_create(self.device, C.byref(self.cfg), C.byref(h)))
+        self.h = h
+
+    def bands(self, short=False):
+        n = (C.c_int * 32)()
+        o = (C.c_int * 32)()
+        nb = check(lib.pac_get_bands(self.h, int(short), n, o))
+        return np.array(n[:nb]), np.array(o[:nb])
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib.pac_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default = {}
+
+
+def default_context(sample_rate=48000, **kw):
+    """Cached context for the stateless drop-in functions (mdct.MDCT ...)."""
+    import torch
+    key = (torch.cuda.current_device() if torch.cuda.is_available() else -1, sample_rate,
+           tuple(sorted(kw.items())))
+    if key not in _default:
+        _default[key] = Context(sample_rate=sample_rate, **kw)
+    return _default[key]
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

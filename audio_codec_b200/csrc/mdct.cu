@@ -1,0 +1,149 @@
+// Batched window+MDCT and IMDCT+window+overlap-add kernels (fp32 and fp64).
+// Replaces coder/mdct.py:43-76 + coder/window.py for whole streams at once:
+// rows are (stream, channel) pairs, frames are hop-N/2 views into each row,
+// so no overlapped copy of the PCM is ever materialised.
+#include "mdct.cuh"
+#include "pac_api.h"
+
+// ---------------------------------------------------------------- forward
+// One CTA transforms FPC consecutive frames of one row: it stages (FPC+1)*M
+// samples once (each sample is fetched from HBM once per CTA, the 1-block halo
+// comes from L2), folds with the window, runs FPC N/4-point FFTs side by side
+// in shared memory and writes M coefficients per frame, coalesced.
+template <typename T, int N, int FPC, int NT>
+__global__ void __launch_bounds__(NT)
+k_mdct_fwd(const T* __restrict__ x, long long rowStride, int nFrames, int groupsPerRow,
+           const T* __restrict__ winTab, int shape, const cplx<T>* __restrict__ tw,
+           const cplx<T>* __restrict__ roots, T* __restrict__ out) {
+    constexpr int M = N / 2, Q = N / 4;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* xs = reinterpret_cast<T*>(smem_raw);                       // [(FPC+1)*M]
+    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(xs + (FPC + 1) * M); // [FPC][Q]
+    const int tid = threadIdx.x;
+    const int row = blockIdx.x / groupsPerRow;
+    const int f0 = (blockIdx.x - row * groupsPerRow) * FPC;
+    const int nf = min(FPC, nFrames - f0);
+    const T* src = x + (long long)row * rowStride + (long long)f0 * M;
+    const int nS = (nf + 1) * M;
+    for (int i = tid; i < (FPC + 1) * M; i += NT) xs[i] = i < nS ? src[i] : (T)0;
+    __syncthreads();
+    mdct_fold<T, N, FPC, NT>(xs, M, winTab, nullptr, shape, tw, fbuf, tid);
+    __syncthreads();
+    cta_fft<T, Q, FPC, NT>(fbuf, roots, tid);
+    mdct_post<T, N, FPC, NT>(fbuf, tw, (T)2 / (T)N, xs, tid);
+    __syncthreads();
+    T* dst = out + ((long long)row * nFrames + f0) * M;
+    for (int i = tid; i < nf * M; i += NT) dst[i] = xs[i];
+}
+
+// ---------------------------------------------------------------- inverse
+// One CTA produces FPC consecutive output blocks (M samples each) of one row.
+// Output block b = windowed IMDCT(frame b-1)[M:] + windowed IMDCT(frame b)[:M],
+// so the CTA inverts frames b0-1 .. b0+FPC-1 (FPC+1 transforms; the extra one is
+// an L2 hit) and overlap-adds in shared memory (coder/pacfile.py:289-295).
+template <typename T, int N, int FPC, int NT>
+__global__ void __launch_bounds__(NT)
+k_imdct_ola(const T* __restrict__ X, int nFrames, int groupsPerRow, const T* __restrict__ winTab, int shape,
+            const cplx<T>* __restrict__ tw, const cplx<T>* __restrict__ roots, T* __restrict__ y,
+            long long rowStride) {
+    constexpr int M = N / 2, Q = N / 4, B = FPC + 1;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* v = reinterpret_cast<T*>(smem_raw);                 // [B][M] coefficients, then DCT-IV output
+    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(v + B * M);  // [B][Q]
+    const int tid = threadIdx.x;
+    const int row = blockIdx.x / groupsPerRow;
+    const int b0 = (blockIdx.x - row * groupsPerRow) * FPC;   // first output block
+    const int nOut = min(FPC, nFrames + 1 - b0);
+    // slot s holds frame b0-1+s
+    const T* src = X + (long long)row * nFrames * M;
+    for (int i = tid; i < B * M; i += NT) {
+        int s = i / M, f = b0 - 1 + s;
+        v[i] = (f >= 0 && f < nFrames) ? src[(long long)f * M + (i - s * M)] : (T)0;
+    }
+    __syncthreads();
+    imdct_pre<T, N, B, NT>(v, (T)1, tw, fbuf, tid);
+    __syncthreads();
+    cta_fft<T, Q, B, NT>(fbuf, roots, tid);
+    mdct_post<T, N, B, NT>(fbuf, tw, (T)1, v, tid);
+    __syncthreads();
+    const T* w = winTab ? winTab + shape * N : nullptr;
+    T* dst = y + (long long)row * rowStride + (long long)b0 * M;
+    for (int i = tid; i < nOut * M; i += NT) {
+        int s = i / M, n = i - s * M;
+        T a = imdct_sample<T, N>(v + s * M, M + n);        // tail of frame b0-1+s
+        T c = imdct_sample<T, N>(v + (s + 1) * M, n);      // head of frame b0+s
+        if (w) { a *= w[M + n]; c *= w[n]; }
+        dst[i] = a + c;
+    }
+}
+
+template <typename T> static const PacTables<T>& tabs(const pac_ctx* c);
+template <> const PacTables<float>& tabs<float>(const pac_ctx* c) { return c->host.f; }
+template <> const PacTables<double>& tabs<double>(const pac_ctx* c) { return c->host.d; }
+
+template <typename T, int N>
+static int launch_fwd(pac_ctx* ctx, const void* x, long long rowStride, int nRows, int nFrames, int window,
+                      void* coefs, cudaStream_t st) {
+    constexpr int FPC = (N == 2048) ? 4 : 16, NT = 256, M = N / 2, Q = N / 4;
+    const PacTables<T>& t = tabs<T>(ctx);
+    const T* win = window == PAC_WIN_NONE ? nullptr : (N == 2048 ? t.win_long : t.win_short);
+    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(N == 2048 ? t.tw_mdct_long : t.tw_mdct_short);
+    const cplx<T>* roots = reinterpret_cast<const cplx<T>*>(t.tw_fft[N == 2048 ? 2 : 0]);
+    int groups = (nFrames + FPC - 1) / FPC;
+    size_t smem = sizeof(T) * ((FPC + 1) * M + 2 * FPC * Q);
+    auto kern = k_mdct_fwd<T, N, FPC, NT>;
+    PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<nRows * groups, NT, smem, st>>>((const T*)x, rowStride, nFrames, groups, win, window, tw, roots,
+                                             (T*)coefs);
+    PAC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+template <typename T, int N>
+static int launch_inv(pac_ctx* ctx, const void* X, int nRows, int nFrames, int window, void* y,
+                      long long rowStride, cudaStream_t st) {
+    constexpr int FPC = (N == 2048) ? 4 : 16, NT = 256, M = N / 2, Q = N / 4, B = FPC + 1;
+    const PacTables<T>& t = tabs<T>(ctx);
+    const T* win = window == PAC_WIN_NONE ? nullptr : (N == 2048 ? t.win_long : t.win_short);
+    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(N == 2048 ? t.tw_mdct_long : t.tw_mdct_short);
+    const cplx<T>* roots = reinterpret_cast<const cplx<T>*>(t.tw_fft[N == 2048 ? 2 : 0]);
+    int groups = (nFrames + 1 + FPC - 1) / FPC;
+    size_t smem = sizeof(T) * (B * M + 2 * B * Q);
+    auto kern = k_imdct_ola<T, N, FPC, NT>;
+    PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<nRows * groups, NT, smem, st>>>((const T*)X, nFrames, groups, win, window, tw, roots, (T*)y, rowStride);
+    PAC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pac_mdct_forward(pac_ctx* ctx, int dtype, const void* x, long long row_stride, int n_rows,
+                                int n_frames, int N, int window, void* coefs, void* stream) {
+    if (!ctx) return PAC_ERR_ARG;
+    if (n_rows <= 0 || n_frames <= 0) return 0;
+    if (!x || !coefs) return PAC_ERR_ARG;
+    if (window < 0 || window > PAC_WIN_NONE) return PAC_ERR_ARG;
+    if (N == 256 && !(window == PAC_WIN_SINE || window == PAC_WIN_KAISER || window == PAC_WIN_NONE)) return PAC_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    if (N == 2048 && dtype == PAC_F32) return launch_fwd<float, 2048>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
+    if (N == 2048 && dtype == PAC_F64) return launch_fwd<double, 2048>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
+    if (N == 256 && dtype == PAC_F32) return launch_fwd<float, 256>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
+    if (N == 256 && dtype == PAC_F64) return launch_fwd<double, 256>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
+    return PAC_ERR_ARG;
+}
+
+extern "C" int pac_imdct_ola(pac_ctx* ctx, int dtype, const void* coefs, int n_rows, int n_frames, int N,
+                             int window, void* y, long long row_stride, void* stream) {
+    if (!ctx) return PAC_ERR_ARG;
+    if (n_rows <= 0 || n_frames <= 0) return 0;
+    if (!y || !coefs) return PAC_ERR_ARG;
+    if (window < 0 || window > PAC_WIN_NONE) return PAC_ERR_ARG;
+    if (N == 256 && !(window == PAC_WIN_SINE || window == PAC_WIN_KAISER || window == PAC_WIN_NONE)) return PAC_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    if (N == 2048 && dtype == PAC_F32) return launch_inv<float, 2048>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
+    if (N == 2048 && dtype == PAC_F64) return launch_inv<double, 2048>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
+    if (N == 256 && dtype == PAC_F32) return launch_inv<float, 256>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
+    if (N == 256 && dtype == PAC_F64) return launch_inv<double, 256>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
+    return PAC_ERR_ARG;
+}

@@ -1,0 +1,71 @@
+/* pac_b200.h -- C ABI of libpac_b200.so, the B200 (sm_100a) implementation of the
+ * Music-422 perceptual coder hot path (Abhipray/audio-codec, coder/*.py).
+ *
+ * The reference is pure Python with no FFI of its own: its boundary is the
+ * Python function surface.  Every entry point below names the
+ * reference function(s) it replaces; audio_codec_b200/*.py binds them with
+ * ctypes under the reference's own module / function names.
+ *
+ * Conventions: plain pointers and sizes only; `stream` is a cudaStream_t passed
+ * as void* (NULL = default stream); buffers named d_* are DEVICE pointers owned
+ * by the caller, h_* are HOST pointers; every function returns 0 or a negative
+ * pac_status; nothing throws.  One context per GPU; a context is immutable after
+ * pac_create and calls on distinct streams/buffers are re-entrant.
+ */
+#ifndef PAC_B200_H
+#define PAC_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pac_ctx pac_ctx;
+
+enum pac_dtype { PAC_F32 = 0, PAC_F64 = 1 };
+enum pac_status {
+    PAC_OK = 0,
+    PAC_ERR_ARG = -1,        /* bad argument */
+    PAC_ERR_ALLOC = -2,      /* device/host allocation failed */
+    PAC_ERR_UNSUPPORTED = -3,/* e.g. block floating point + SBR (crashes in the reference too) */
+    PAC_ERR_SOFT = -4        /* per-frame soft error flagged on device (see pac_encode flags) */
+    /* <= -1000: -(cudaError_t) - 1000 */
+};
+/* window shapes: coder/window.py:14 SineWindow, :61 StartWindow, :73 StopWindow,
+ * :82 StartStopWindow, :45 KBDWindow (a Kaiser window, alpha = 4), none */
+enum pac_window { PAC_W_SINE = 0, PAC_W_START = 1, PAC_W_STOP = 2, PAC_W_STARTSTOP = 3, PAC_W_KAISER = 4, PAC_W_NONE = 5 };
+
+/* The fields of the reference's CodingParams bag the path reads
+ * (coder/pacfile.py:157-174, :699-707). */
+typedef struct pac_config {
+    int sample_rate;            /* Hz */
+    int n_channels;
+    int n_mdct_lines;           /* 1024 (long); short blocks are always 128 */
+    int n_scale_bits;           /* 4 */
+    int n_mant_size_bits;       /* 12 */
+    int use_sbr;                /* coder/pacfile.py:704 */
+    int use_vq;                 /* coder/pacfile.py:705 */
+    double target_bits_per_sample; /* rate_kbps / (fs/1000), per channel (pacfile.py:702) */
+} pac_config;
+
+int pac_create(int device, const pac_config* cfg, pac_ctx** out);
+void pac_destroy(pac_ctx* ctx);
+const char* pac_strerror(int status);
+/* band layout as ScaleFactorBands(AssignMDCTLinesFromFreqLimits(..)) builds it
+ * (coder/psychoac.py:106-160); which = 0 long, 1 short.  Returns nBands. */
+int pac_get_bands(const pac_ctx* ctx, int which, int* n_lines, int* omitted);
+
+/* mdct.MDCT / window.* (coder/mdct.py:63-69, coder/codec.py:303-305), batched.
+ * d_x: n_rows rows of (n_frames+1)*N/2 samples, row pitch row_stride elements;
+ * frame f of a row is samples [f*N/2, f*N/2+N).  d_coefs: [n_rows][n_frames][N/2].
+ * N is 2048 or 256. */
+int pac_mdct_forward(pac_ctx* ctx, int dtype, const void* d_x, long long row_stride, int n_rows,
+                     int n_frames, int N, int window, void* d_coefs, void* stream);
+/* mdct.IMDCT + synthesis window + overlap-add (coder/mdct.py:56-62,
+ * coder/codec.py:88-89, coder/pacfile.py:289-295).  d_y: n_rows rows of
+ * (n_frames+1)*N/2 samples. */
+int pac_imdct_ola(pac_ctx* ctx, int dtype, const void* d_coefs, int n_rows, int n_frames, int N,
+                  int window, void* d_y, long long row_stride, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -110,8 +110,39 @@ def block_flags(x, n_blocks):
             for k in range(n_blocks)]
 
 
-def encode_pcm(pcm, fs, rate_kbps, use_vq=True, use_sbr=None):
-    """int16 PCM [C, n] -> .pac bytes, as coder/pacfile.py:674-756 ("Encode")."""
+def read_wav_like_reference(path):
+    """16-bit WAV -> (fs, pcm[C, n_read], n_header) the way the reference reads it.
+
+    coder/pcmfile.py:32-64 takes numSamples from the data-chunk size, but
+    PACFile.WriteFileHeader (coder/pacfile.py:309-315) then ADDS up to 2048 to
+    that same codingParams.numSamples before the read loop runs, so
+    PCMFile.ReadDataBlock (:66-77) keeps reading past the data chunk: any
+    trailing RIFF chunk bytes are coded as if they were PCM (harpsichord.wav
+    has 168 such bytes).  n_header is the data-chunk count the header is
+    computed from."""
+    raw = open(path, "rb").read()
+    assert raw[:4] == b"RIFF" and raw[8:12] == b"WAVE"
+    pos = 12
+    while raw[pos:pos + 4] != b"fmt ":
+        pos += 4
+    _, tag, C, fs, _, _, bps = struct.unpack_from("<LHHLLHH", raw, pos + 4)
+    assert tag == 1 and bps == 16
+    pos += 24
+    while raw[pos:pos + 4] != b"data":
+        pos += 4
+    n = struct.unpack_from("<L", raw, pos + 4)[0] // (C * 2)
+    pos += 8
+    n_inflated = n + 1024 + (1024 if n % 1024 == 0 else 0)
+    body = raw[pos:pos + n_inflated * C * 2]
+    body = body + b"\0" * (-len(body) % (2 * C))          # short read is zero padded (:78-80)
+    pcm = np.frombuffer(body, dtype="<i2").reshape(-1, C).T.copy()
+    return fs, pcm, n
+
+
+def encode_pcm(pcm, fs, rate_kbps, use_vq=True, use_sbr=None, header_samples=None):
+    """int16 PCM [C, n] -> .pac bytes, as coder/pacfile.py:674-756 ("Encode").
+    header_samples: sample count the header is derived from when it differs
+    from pcm.shape[1] (see read_wav_like_reference)."""
     pcm = np.asarray(pcm)
     C, n = pcm.shape
     p = codec.Params(fs, rate_kbps, C, use_vq, use_sbr)
@@ -119,7 +150,7 @@ def encode_pcm(pcm, fs, rate_kbps, use_vq=True, use_sbr=None):
     x = np.zeros((C, nb * 1024))
     x[:, :n] = dsp.pcm_to_float(pcm)
     det = block_flags(x, nb)
-    out = [header(p, n)]
+    out = [header(p, n if header_samples is None else header_samples)]
     prior = [np.zeros(1024) for _ in range(C)]
     last = cur = False
     # blocks 0..nb-1, then the last block AGAIN (:725-743), then Close's zeros
