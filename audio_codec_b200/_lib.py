@@ -40,6 +40,9 @@ def _load():
         "pac_get_bands": (i, [vp, i, C.POINTER(i), C.POINTER(i)]),
         "pac_mdct_forward": (i, [vp, i, vp, ll, i, i, i, i, vp, vp]),
         "pac_imdct_ola": (i, [vp, i, vp, i, i, i, i, vp, ll, vp]),
+        "pac_header_bytes": (i, [vp]),
+        "pac_encode_bound": (ll, [vp, C.POINTER(i), i]),
+        "pac_encode_streams": (i, [vp, vp, C.POINTER(i), C.POINTER(i), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -49,7 +52,8 @@ def _load():
 
 
 lib = _load()
-EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola"]
+EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola",
+           "pac_header_bytes", "pac_encode_bound", "pac_encode_streams"]
 
 
 def check(rc):

@@ -1,0 +1,613 @@
+// Fused stream encoder: PCM -> .pac bytes, all stages on device.
+//
+//   k_transient   per PCM block: peak-to-average transient verdict
+//                 (coder/detect_transients.py:5-23 on [block || zeros], pacfile.py:717-731)
+//   k_encode      one CTA per written channel-block: window + MDCT, overall scale,
+//                 psychoacoustic SMRs, bit allocation, PVQ / block-FP quantisation,
+//                 MSB-first bit packing into a fixed-stride scratch record
+//                 (coder/codec.py:266-380, :426-555; coder/pacfile.py:363-447)
+//   k_sizes/scan/k_gather  byte layout of the variable-length records with their
+//                 4-byte length prefixes (coder/pacfile.py:550-608)
+//
+// Stream layout: stream s owns nb[s] PCM blocks of 1024 samples per channel,
+// planar int16 at element offset (blkOff[s]*C + c*nb[s])*1024, zero padded to a
+// whole block.  It produces nb[s]+2 written blocks: 0..nb-1, the last block AGAIN
+// (pacfile.py:725-743), then Close()'s zero block (pacfile.py:612-625).
+#include <cub/device/device_scan.cuh>
+#include "bitalloc.cuh"
+#include "mdct.cuh"
+#include "pac_api.h"
+#include "psy.cuh"
+#include "pvq.cuh"
+
+#define ENC_NT 256
+#define REC_STRIDE 2176          // bytes per channel-block scratch record (>= worst-case declared size)
+#define REC_WORDS (REC_STRIDE / 4)
+#define BAND_WORDS 640
+
+// int16 PCM -> signed fraction (coder/pcmfile.py:89-98): 2|c|/65535 with the sign
+// restored; -32768 has magnitude bits 0 and maps to 0.0.
+__device__ __forceinline__ double pcm_to_double(short c) {
+    int m = c < 0 ? -(int)c : (int)c;
+    m &= 0x7fff;
+    double v = (double)(2 * m) / 65535.0;
+    return c < 0 ? -v : v;
+}
+
+// ---------------------------------------------------------------- transient detector
+// One CTA (128 threads) per PCM block, all channels.  Exact integer form of
+// mymax/avg > 4.5 with avg = mean(|x[:, :n]|), n = min(max_c(argmax_c)+500, 2048):
+//   2*cmax_c*(C*n) > 9*sum|c|   (the second half of the look-ahead is always zero).
+__global__ void __launch_bounds__(128)
+k_transient(const short* __restrict__ pcm, const int* __restrict__ blkOff, const int* __restrict__ nb, int nStreams,
+            int C, unsigned char* __restrict__ det) {
+    __shared__ int s_max[8][4], s_arg[8][4];
+    __shared__ unsigned long long s_sum[4];
+    __shared__ int s_n;
+    const int g = blockIdx.x;                 // global PCM block index
+    int lo = 0, hi = nStreams;                // stream with blkOff[s] <= g < blkOff[s+1]
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (blkOff[mid] <= g) lo = mid; else hi = mid;
+    }
+    const int s = lo, k = g - blkOff[s], nbs = nb[s];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int cmaxAll[8], amaxAll[8];
+    for (int c = 0; c < C && c < 8; ++c) {
+        const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
+        int best = -1, arg = 0;
+        for (int i = tid; i < 1024; i += 128) {
+            int v = p[i];
+            v = (v < 0 ? -v : v) & 0x7fff;
+            if (v > best) { best = v; arg = i; }
+        }
+        for (int o = 16; o; o >>= 1) {
+            int ob = __shfl_xor_sync(0xffffffffu, best, o), oa = __shfl_xor_sync(0xffffffffu, arg, o);
+            if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+        }
+        if (lane == 0) { s_max[c][warp] = best; s_arg[c][warp] = arg; }
+    }
+    __syncthreads();
+    int nmax = 0;
+    for (int c = 0; c < C && c < 8; ++c) {
+        int best = s_max[c][0], arg = s_arg[c][0];
+        for (int w = 1; w < 4; ++w)
+            if (s_max[c][w] > best || (s_max[c][w] == best && s_arg[c][w] < arg)) { best = s_max[c][w]; arg = s_arg[c][w]; }
+        cmaxAll[c] = best;
+        amaxAll[c] = arg;
+        nmax = max(nmax, arg + 500);
+    }
+    const int n = min(nmax, 2048);
+    const int nn = min(n, 1024);
+    unsigned long long sum = 0;
+    for (int c = 0; c < C && c < 8; ++c) {
+        const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
+        for (int i = tid; i < nn; i += 128) {
+            int v = p[i];
+            sum += (unsigned long long)((v < 0 ? -v : v) & 0x7fff);
+        }
+    }
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) s_sum[warp] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long S = s_sum[0] + s_sum[1] + s_sum[2] + s_sum[3];
+        bool t = false;
+        if (S != 0)
+            for (int c = 0; c < C && c < 8; ++c)
+                if (2ull * (unsigned long long)cmaxAll[c] * (unsigned long long)(C * n) > 9ull * S) t = true;
+        det[g] = t ? 1 : 0;
+        (void)amaxAll; (void)s_n;
+    }
+}
+
+// ---------------------------------------------------------------- per-frame encode
+struct EncSmem {
+    double* xs;        // [2048] frame samples; later PVQ workspace A
+    double* fb;        // [2048] FFT buffer / masker list; later PVQ workspace B
+    double* lines;     // [1024] MDCT lines (scaled)
+    double* mk;        // [1040] |X| -> intensity -> masked threshold; later PVQ pulse ints
+    double* smr;       // [32]
+    double* tmp;       // [32]
+    unsigned* blockbuf;  // [REC_WORDS] the channel-block bitstream (big-endian words)
+    unsigned* bandbits;  // [BAND_WORDS] per-band private bit buffers
+    int* ba;           // [32] bit allocation
+    int* nlEff;        // [32] lines per band as the allocator sees them (1 for SBR-omitted)
+    int* used;         // [32] bits emitted per band
+    int* wordOff;      // [33]
+    int* capOff;       // [33] pow2 workspace offsets
+    int* sfb;          // [32] BFP scale factors
+    int* misc;         // [16]
+    double* red;       // [16] reduction scratch
+    double* env;       // [32] SBR: sum of |X|/H over each omitted band
+};
+
+__device__ __forceinline__ double block_max(double v, double* red, int tid) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        double t = __shfl_xor_sync(0xffffffffu, v, o);
+        v = t > v ? t : v;
+    }
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    double r = red[0];
+#pragma unroll
+    for (int w = 1; w < ENC_NT / 32; ++w) r = red[w] > r ? red[w] : r;
+    return r;
+}
+
+// Encode one frame of N samples at fx (shared) and append its fields to the block
+// bitstream at bit position *bpos.  Returns the DECLARED size in bits
+// (getNumBytesNeeded, coder/pacfile.py:342-361).  sbr: long frame of an SBR stream.
+template <int N>
+__device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const double* fx, int shape, bool cur,
+                            bool lastOrNext, bool sbr, int* bpos, int* err) {
+    constexpr int H = N / 2, Q = N / 4;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
+    const int nB = bands.nBands;
+    const PsyConst pc = psy_const<N>(dev);
+    const double* winTab = (N == PAC_NLONG) ? dev->d.win_long : dev->d.win_short;
+    const cplx<double>* tw = reinterpret_cast<const cplx<double>*>(N == PAC_NLONG ? dev->d.tw_mdct_long : dev->d.tw_mdct_short);
+    const cplx<double>* rootsQ = reinterpret_cast<const cplx<double>*>(dev->d.tw_fft[N == PAC_NLONG ? 2 : 0]);
+    cplx<double>* fbuf = reinterpret_cast<cplx<double>*>(S.fb);
+
+    // (1) window + MDCT (coder/codec.py:301-305)
+    mdct_fold<double, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
+    __syncthreads();
+    cta_fft<double, Q, 1, ENC_NT>(fbuf, rootsQ, tid);
+    mdct_post<double, N, 1, ENC_NT>(fbuf, tw, 2.0 / (double)N, S.lines, tid);
+    __syncthreads();
+    double mx = 0.0;
+    for (int i = tid; i < H; i += ENC_NT) mx = fmax(mx, fabs(S.lines[i]));
+    double maxLine = block_max(mx, S.red, tid);
+
+    // (2) Hann FFT magnitude (shared by the psychoacoustic model and the SBR envelope)
+    hann_rfft_mag<N, ENC_NT>(fx, pc, fbuf, S.mk, tid);
+    if (sbr) {                                    // coder/codec.py:460-473
+        double m2 = 0.0;
+        for (int k = tid; k <= H; k += ENC_NT) m2 = fmax(m2, S.mk[k]);
+        double maxFFT = block_max(m2, S.red, tid) / (double)H;
+        maxLine = fmax(maxLine, maxFFT);
+        // per omitted band: sum of fftLines = |X|/H over the band (scale applied later, exact)
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            if (!bands.omitted[b]) continue;
+            double a = 0.0;
+            for (int i = lane; i < bands.nLines[b]; i += 32) a += S.mk[bands.lower[b] + i] / (double)H;
+            a = warp_sum(a);
+            if (lane == 0) S.env[b] = a;
+        }
+        __syncthreads();
+    }
+    const int scale = scale_factor(maxLine, dev->nScaleBits, 5);      // codec.py:308-311 (default nMantBits)
+    const double up = (double)(1 << scale);
+    for (int i = tid; i < H; i += ENC_NT) S.lines[i] *= up;
+    for (int k = tid; k <= H; k += ENC_NT) {
+        double m = S.mk[k];
+        S.mk[k] = pc.norm * (m * m);
+    }
+    __syncthreads();
+
+    // (3) psychoacoustic model -> SMR per band
+    double* mz = S.fb;
+    double* ms = S.fb + 640;
+    double* mkk = S.fb + 1280;
+    pick_maskers<N, ENC_NT>(S.mk, pc, mz, ms, mkk, &S.misc[0], tid);
+    const int nMask = S.misc[0];
+    masked_threshold<N, ENC_NT>(pc, mz, ms, mkk, nMask, S.mk, tid);
+    band_smr<ENC_NT>(S.lines, scale, S.mk, bands, S.smr, tid);
+
+    // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)
+    if (tid < nB) S.nlEff[tid] = (sbr && bands.omitted[tid]) ? 1 : bands.nLines[tid];
+    __syncthreads();
+    if (warp == 0) {
+        int nfb = H;
+        if (!sbr) {
+            if (cur) nfb = (int)(1.45 * H);
+            if (lastOrNext) nfb = (int)(0.85 * nfb);
+        }
+        double budget = dev->targetBitsPerSample * (double)nfb;
+        if (dev->useVQ) budget -= (double)dev->nScaleBits;
+        else budget -= (double)(dev->nScaleBits * (nB + 1));
+        budget -= (double)(dev->nMantSizeBits * nB);
+        warp_bit_alloc(budget, dev->maxMantBits, nB, S.nlEff, S.smr, S.tmp, S.ba);
+    }
+    __syncthreads();
+
+    // (5) quantise each coded band into its private bit buffer
+    if (tid == 0) {
+        int w = 0, c = 0;
+        for (int b = 0; b < nB; ++b) {
+            S.wordOff[b] = w;
+            S.capOff[b] = c;
+            int bits = S.ba[b] * S.nlEff[b];
+            w += (bits + 31) / 32 + 3;                    // slack: a 64-bit put may straddle
+            int cap = 1;
+            while (cap < bands.nLines[b]) cap <<= 1;
+            c += cap;
+        }
+        S.wordOff[nB] = w;
+        S.capOff[nB] = c;
+        if (w > BAND_WORDS || c > (N == PAC_NLONG ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
+    }
+    for (int i = tid; i < BAND_WORDS; i += ENC_NT) S.bandbits[i] = 0u;
+    __syncthreads();
+    if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (N == PAC_NLONG ? 2048 : 256)) return 0;
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab};
+    int* yws = reinterpret_cast<int*>(S.mk);              // masked threshold is dead from here on
+    // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
+    // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
+    double* wsA = (N == PAC_NLONG) ? S.xs : S.lines + 256;
+    double* wsB = (N == PAC_NLONG) ? S.fb : S.lines + 512;
+    if (dev->useVQ) {
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            int used = 0;
+            if (S.ba[b]) {
+                const int cap = S.capOff[b + 1] - S.capOff[b];
+                BitW bw = {S.bandbits + S.wordOff[b], 0};
+                int werr = 0;
+                if (sbr && bands.omitted[b]) {
+                    // one value: mean |fftLines| of the band (coder/codec.py:508-510)
+                    __shared__ double s_env[ENC_NT / 32];
+                    if (lane == 0) s_env[warp] = (S.env[b] * up) / (double)bands.nLines[b];
+                    __syncwarp();
+                    used = warp_quantize_gain_shape(pt, &s_env[warp], 1, S.ba[b], wsA + S.capOff[b],
+                                                    wsB + S.capOff[b], yws + S.capOff[b], cap, bw, &werr);
+                } else {
+                    used = warp_quantize_gain_shape(pt, S.lines + bands.lower[b], bands.nLines[b],
+                                                    S.ba[b] * bands.nLines[b], wsA + S.capOff[b],
+                                                    wsB + S.capOff[b], yws + S.capOff[b], cap, bw, &werr);
+                }
+                if (werr && lane == 0) atomicOr(err, werr);
+            }
+            if (lane == 0) {
+                S.used[b] = used;
+                if (used == 0) S.ba[b] = 0;               // coder/codec.py:352-353
+            }
+        }
+    } else {
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            const int lo = bands.lower[b], n = bands.nLines[b], bb = S.ba[b];
+            double m = 0.0;
+            for (int i = lane; i < n; i += 32) m = fmax(m, fabs(S.lines[lo + i]));
+#pragma unroll
+            for (int o = 16; o; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+            const int sf = scale_factor(m, dev->nScaleBits, bb);       // coder/codec.py:369-371
+            if (bb)
+                for (int i = lane; i < n; i += 32)
+                    bw_put_at(S.bandbits + S.wordOff[b], i * bb,
+                              mantissa_bfp(S.lines[lo + i], sf, dev->nScaleBits, bb), bb);
+            if (lane == 0) {
+                S.sfb[b] = sf;
+                S.used[b] = bb * n;
+            }
+        }
+    }
+    __syncthreads();
+
+    // (6) frame header + band payload positions (coder/pacfile.py:363-447), thread 0
+    if (tid == 0) {
+        BitW bw = {S.blockbuf, *bpos};
+        bw_put(bw, (unsigned long long)scale, dev->nScaleBits);
+        int declared = dev->nScaleBits;
+        if (dev->useVQ)
+            for (int b = 0; b < nB; ++b) bw_put(bw, S.ba[b] ? S.ba[b] - 1 : 0, dev->nMantSizeBits);
+        for (int b = 0; b < nB; ++b) {
+            if (!dev->useVQ) {
+                bw_put(bw, S.ba[b] ? S.ba[b] - 1 : 0, dev->nMantSizeBits);
+                bw_put(bw, (unsigned long long)S.sfb[b], dev->nScaleBits);
+            }
+            int u = S.ba[b] ? S.used[b] : 0;
+            S.capOff[b] = bw.pos;                         // reuse: destination bit position of band b
+            bw.pos += u;
+            declared += dev->nMantSizeBits + dev->nScaleBits;
+            if (S.ba[b]) declared += (sbr && bands.omitted[b]) ? S.ba[b] : S.ba[b] * bands.nLines[b];
+        }
+        *bpos = bw.pos;
+        S.misc[2] = declared;
+    }
+    __syncthreads();
+    // (7) merge the band buffers into the block bitstream (disjoint bit ranges)
+    for (int b = warp; b < nB; b += ENC_NT / 32) {
+        const int u = S.ba[b] ? S.used[b] : 0;
+        const unsigned* src = S.bandbits + S.wordOff[b];
+        for (int i = lane; i * 32 < u; i += 32) {
+            int nb = min(32, u - i * 32);
+            bw_put_at(S.blockbuf, S.capOff[b] + i * 32, (unsigned long long)(src[i] >> (32 - nb)), nb);
+        }
+    }
+    __syncthreads();
+    return S.misc[2];
+}
+
+// ---------------------------------------------------------------- block kernel
+struct EncArgs {
+    const short* pcm;
+    const int* blkOff;     // [S+1] PCM block prefix
+    const int* nb;         // [S]
+    const int* wbOff;      // [S+1] written-block prefix (nb+2 each)
+    const unsigned char* det;
+    int nStreams;
+    unsigned char* rec;    // [nChBlocks][REC_STRIDE]
+    int* recBytes;         // [nChBlocks] declared byte size
+    unsigned char* zeroSub;// [nChBlocks] 1 if a short sub-frame of this channel is all zero
+    int* err;              // [1] OR of soft error flags
+};
+
+__global__ void __launch_bounds__(ENC_NT)
+k_encode(const PacDev* __restrict__ dev, EncArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EncSmem S;
+    double* dp = reinterpret_cast<double*>(smem_raw);
+    S.xs = dp; dp += 2048;
+    S.fb = dp; dp += 2048;
+    S.lines = dp; dp += 1024;
+    S.mk = dp; dp += 1040;
+    S.smr = dp; dp += 32;
+    S.tmp = dp; dp += 32;
+    S.red = dp; dp += 16;
+    S.env = dp; dp += 32;
+    unsigned* up = reinterpret_cast<unsigned*>(dp);
+    S.blockbuf = up; up += REC_WORDS;
+    S.bandbits = up; up += BAND_WORDS;
+    int* ip = reinterpret_cast<int*>(up);
+    S.ba = ip; ip += 32;
+    S.nlEff = ip; ip += 32;
+    S.used = ip; ip += 32;
+    S.wordOff = ip; ip += 34;
+    S.capOff = ip; ip += 34;
+    S.sfb = ip; ip += 32;
+    S.misc = ip; ip += 16;
+
+    const int tid = threadIdx.x;
+    const int C = dev->nChannels;
+    const int cb = blockIdx.x;                // written channel-block index
+    const int wb = cb / C, c = cb - wb * C;   // written block (global), channel
+    int lo = 0, hi = a.nStreams;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (a.wbOff[mid] <= wb) lo = mid; else hi = mid;
+    }
+    const int s = lo, j = wb - a.wbOff[s], nbs = a.nb[s];
+    const unsigned char* det = a.det + a.blkOff[s];
+    // flags (coder/pacfile.py:717-743): written block j carries next = det[j], cur = det[j-1],
+    // last = det[j-2]; the duplicate of the last block has next = False; Close()'s block has none.
+    bool nxt = j < nbs && det[j];
+    bool cur = j >= 1 && j - 1 < nbs && det[j - 1];
+    bool last = j >= 2 && j - 2 < nbs && det[j - 2];
+    if (j == nbs + 1) nxt = cur = last = false;
+    const int dataBlk = j < nbs ? j : (j == nbs ? nbs - 1 : -1);
+    const int priorBlk = j == 0 ? -1 : min(j - 1, nbs - 1);
+    const short* base = a.pcm + ((long long)a.blkOff[s] * C + (long long)c * nbs) * 1024;
+    for (int i = tid; i < 2048; i += ENC_NT) {
+        int blk = i < 1024 ? priorBlk : dataBlk;
+        S.xs[i] = blk < 0 ? 0.0 : pcm_to_double(base[(long long)blk * 1024 + (i & 1023)]);
+    }
+    for (int i = tid; i < REC_WORDS; i += ENC_NT) S.blockbuf[i] = 0u;
+    if (tid == 0) {
+        S.misc[3] = 0;
+        S.misc[4] = 0;
+    }
+    __syncthreads();
+    if (tid == 0) {                           // 3 flag bits (coder/pacfile.py:575-577)
+        BitW bw = {S.blockbuf, 0};
+        bw_put(bw, last, 1);
+        bw_put(bw, cur, 1);
+        bw_put(bw, nxt, 1);
+        S.misc[3] = bw.pos;
+    }
+    __syncthreads();
+    int declared = 4;                         // "+4 for block switching" (pacfile.py:560)
+    if (!cur) {
+        int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
+        declared += encode_frame<PAC_NLONG>(dev, S, S.xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err);
+    } else {
+        // zero sub-frame check (coder/pacfile.py:503-506): the block is dropped if ANY channel has one
+        for (int sf = 0; sf < PAC_SUBFRAMES; ++sf) {
+            bool nz = false;
+            for (int i = tid; i < PAC_NSHORT; i += ENC_NT) nz |= S.xs[448 + 128 * sf + i] != 0.0;
+            if (!__syncthreads_or(nz) && tid == 0) S.misc[4] = 1;
+        }
+        for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
+            declared += encode_frame<PAC_NSHORT>(dev, S, S.xs + 448 + 128 * sf, PAC_WIN_SINE, true, last || nxt, false,
+                                                 &S.misc[3], a.err);
+    }
+    __syncthreads();
+    const int nBytes = (declared + 7) / 8;
+    unsigned* out = reinterpret_cast<unsigned*>(a.rec + (long long)cb * REC_STRIDE);
+    const int nW = min(REC_WORDS, (nBytes + 3) / 4);
+    for (int i = tid; i < nW; i += ENC_NT) out[i] = __byte_perm(S.blockbuf[i], 0, 0x0123);
+    if (tid == 0) {
+        a.recBytes[cb] = nBytes;
+        a.zeroSub[cb] = (unsigned char)S.misc[4];
+        if (nBytes > REC_STRIDE || S.misc[3] > declared) atomicOr(a.err, PVQ_ERR_STACK);
+    }
+}
+
+// ---------------------------------------------------------------- byte layout
+// size of every channel-block in the output: 4 + nBytes, or 0 if its block is
+// dropped (a transient block with an all-zero sub-frame in any channel); the
+// first channel-block of a stream also carries the stream's header bytes.
+__global__ void k_sizes(const int* __restrict__ recBytes, const unsigned char* __restrict__ zeroSub,
+                        const int* __restrict__ wbOff, int nStreams, int C, int headerBytes, int nChBlocks,
+                        long long* __restrict__ sizes) {
+    int cb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cb >= nChBlocks) return;
+    int wb = cb / C;
+    bool drop = false;
+    for (int c = 0; c < C; ++c) drop |= zeroSub[wb * C + c] != 0;
+    long long sz = drop ? 0 : 4 + recBytes[cb];
+    int lo = 0, hi = nStreams;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (wbOff[mid] <= wb) lo = mid; else hi = mid;
+    }
+    if (cb == wbOff[lo] * C) sz += headerBytes;
+    sizes[cb] = sz;
+}
+
+// one warp per channel-block: <L length prefix + payload to its final offset
+__global__ void k_gather(const unsigned char* __restrict__ rec, const int* __restrict__ recBytes,
+                         const long long* __restrict__ sizes, const long long* __restrict__ offs,
+                         const int* __restrict__ wbOff, int nStreams, int C, int headerBytes, int nChBlocks,
+                         unsigned char* __restrict__ out, long long cap, long long* __restrict__ streamOff) {
+    int cb = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (cb >= nChBlocks) return;
+    long long o = offs[cb], sz = sizes[cb];
+    int wb = cb / C;
+    int lo = 0, hi = nStreams;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (wbOff[mid] <= wb) lo = mid; else hi = mid;
+    }
+    if (cb == wbOff[lo] * C) {
+        if (lane == 0) streamOff[lo] = o;
+        o += headerBytes;
+        sz -= headerBytes;
+    }
+    if (cb == nChBlocks - 1 && lane == 0) streamOff[nStreams] = offs[cb] + sizes[cb];
+    if (sz == 0 || o + sz > cap) return;
+    int nBytes = recBytes[cb];
+    if (lane < 4) out[o + lane] = (unsigned char)((unsigned)nBytes >> (8 * lane));
+    const unsigned char* src = rec + (long long)cb * REC_STRIDE;
+    for (int i = lane; i < nBytes; i += 32) out[o + 4 + i] = src[i];
+}
+
+// .pac header (coder/pacfile.py:306-333) with the numSamples rule of :309-315
+__global__ void k_headers(const unsigned char* __restrict__ tmpl, int headerBytes, const int* __restrict__ hdrSamples,
+                          const long long* __restrict__ streamOff, int nStreams, unsigned char* __restrict__ out,
+                          long long cap) {
+    int s = blockIdx.x;
+    long long o = streamOff[s];
+    if (o + headerBytes > cap) return;
+    for (int i = threadIdx.x; i < headerBytes; i += blockDim.x) out[o + i] = tmpl[i];
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        unsigned n = (unsigned)hdrSamples[s];
+        if (n % PAC_HALF_LONG == 0) n += PAC_HALF_LONG;
+        n += PAC_HALF_LONG;
+        out[o + 10 + threadIdx.x] = (unsigned char)(n >> (8 * threadIdx.x));
+    }
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+extern "C" int pac_header_bytes(const pac_ctx* ctx) {
+    return ctx ? 30 + 2 * ctx->host.longBands.nBands : PAC_ERR_ARG;
+}
+
+extern "C" long long pac_encode_bound(const pac_ctx* ctx, const int* h_nblocks, int n_streams) {
+    if (!ctx || !h_nblocks) return PAC_ERR_ARG;
+    long long tot = 0;
+    for (int s = 0; s < n_streams; ++s)
+        tot += pac_header_bytes(ctx) + (long long)(h_nblocks[s] + 2) * ctx->cfg.n_channels * (4 + REC_STRIDE);
+    return tot;
+}
+
+extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h_nblocks, const int* h_hdr_samples,
+                                  int n_streams, unsigned char* d_out, long long out_capacity,
+                                  long long* h_stream_off, int* h_err, void* stream) {
+    if (!ctx || !h_nblocks || !h_hdr_samples || !h_stream_off) return PAC_ERR_ARG;
+    if (n_streams <= 0) return 0;
+    if (!d_pcm || !d_out) return PAC_ERR_ARG;
+    if (ctx->cfg.use_sbr && !ctx->cfg.use_vq) return PAC_ERR_UNSUPPORTED;   // crashes in the reference too
+    cudaStream_t st = (cudaStream_t)stream;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    const int C = ctx->cfg.n_channels, S = n_streams;
+    const int hdrB = pac_header_bytes(ctx);
+    // host-side prefix arrays
+    size_t hostInts = (size_t)4 * (S + 1);
+    void* pin = nullptr;
+    int rc = pac_pinned(ctx, hostInts * sizeof(int) + 128 + (S + 2) * sizeof(long long), &pin);
+    if (rc) return rc;
+    int* hBlkOff = (int*)pin;
+    int* hNb = hBlkOff + (S + 1);
+    int* hWbOff = hNb + (S + 1);
+    int* hHdr = hWbOff + (S + 1);
+    unsigned char* hTmpl = (unsigned char*)(hHdr + (S + 1));
+    long long* hOff = (long long*)(hTmpl + 128);
+    long long totBlk = 0, totWb = 0;
+    for (int s = 0; s < S; ++s) {
+        if (h_nblocks[s] < 1) return PAC_ERR_ARG;
+        hBlkOff[s] = (int)totBlk;
+        hWbOff[s] = (int)totWb;
+        hNb[s] = h_nblocks[s];
+        hHdr[s] = h_hdr_samples[s];
+        totBlk += h_nblocks[s];
+        totWb += h_nblocks[s] + 2;
+        if (totWb * C > 0x7ffffff0LL) return PAC_ERR_ARG;
+    }
+    hBlkOff[S] = (int)totBlk;
+    hWbOff[S] = (int)totWb;
+    hNb[S] = 0;
+    hHdr[S] = 0;
+    {   // header template; numSamples patched per stream on device
+        unsigned char* h = hTmpl;
+        memset(h, 0, 128);
+        memcpy(h, "PAC ", 4);
+        auto p32 = [&](int o, unsigned v) { for (int i = 0; i < 4; ++i) h[o + i] = (unsigned char)(v >> (8 * i)); };
+        auto p16 = [&](int o, unsigned v) { for (int i = 0; i < 2; ++i) h[o + i] = (unsigned char)(v >> (8 * i)); };
+        p32(4, (unsigned)ctx->cfg.sample_rate);
+        p16(8, (unsigned)C);
+        p32(10, 0);
+        p32(14, PAC_HALF_LONG);
+        p16(18, (unsigned)ctx->cfg.n_scale_bits);
+        p16(20, (unsigned)ctx->cfg.n_mant_size_bits);
+        p16(22, ctx->cfg.use_sbr ? 1 : 0);
+        p16(24, ctx->cfg.use_vq ? 1 : 0);
+        p32(26, (unsigned)ctx->host.longBands.nBands);
+        for (int b = 0; b < ctx->host.longBands.nBands; ++b) p16(30 + 2 * b, (unsigned)ctx->host.longBands.nLines[b]);
+    }
+    const long long nCh = totWb * C;
+    // device scratch carve-up
+    size_t tempBytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tempBytes, (long long*)nullptr, (long long*)nullptr, (int)nCh, st);
+    size_t o = 0;
+    auto carve = [&](size_t bytes) { size_t r = o; o += align256(bytes); return r; };
+    size_t oInts = carve(hostInts * sizeof(int) + 128);
+    size_t oDet = carve((size_t)totBlk);
+    size_t oRec = carve((size_t)nCh * REC_STRIDE);
+    size_t oRecB = carve((size_t)nCh * sizeof(int));
+    size_t oZero = carve((size_t)nCh);
+    size_t oSizes = carve((size_t)nCh * sizeof(long long));
+    size_t oOffs = carve((size_t)nCh * sizeof(long long));
+    size_t oSOff = carve((size_t)(S + 2) * sizeof(long long));
+    size_t oErr = carve(sizeof(int));
+    size_t oTemp = carve(tempBytes);
+    void* scr = nullptr;
+    if ((rc = pac_scratch(ctx, o, &scr))) return rc;
+    unsigned char* sb = (unsigned char*)scr;
+    int* dBlkOff = (int*)(sb + oInts);
+    int* dNb = dBlkOff + (S + 1);
+    int* dWbOff = dNb + (S + 1);
+    int* dHdr = dWbOff + (S + 1);
+    unsigned char* dTmpl = (unsigned char*)(dHdr + (S + 1));
+    PAC_CHECK(cudaMemcpyAsync(dBlkOff, hBlkOff, hostInts * sizeof(int) + 128, cudaMemcpyHostToDevice, st));
+    PAC_CHECK(cudaMemsetAsync(sb + oErr, 0, sizeof(int), st));
+    k_transient<<<(unsigned)totBlk, 128, 0, st>>>(d_pcm, dBlkOff, dNb, S, C, sb + oDet);
+    EncArgs a;
+    a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
+    a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
+    size_t smem = (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
+                  (REC_WORDS + BAND_WORDS) * sizeof(unsigned) + (32 * 4 + 34 * 2 + 16) * sizeof(int);
+    PAC_CHECK(cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_encode<<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
+    PAC_CHECK(cudaGetLastError());
+    k_sizes<<<(unsigned)((nCh + 255) / 256), 256, 0, st>>>(a.recBytes, a.zeroSub, dWbOff, S, C, hdrB, (int)nCh,
+                                                           (long long*)(sb + oSizes));
+    PAC_CHECK(cub::DeviceScan::ExclusiveSum(sb + oTemp, tempBytes, (long long*)(sb + oSizes), (long long*)(sb + oOffs),
+                                            (int)nCh, st));
+    k_gather<<<(unsigned)((nCh * 32 + 255) / 256), 256, 0, st>>>(a.rec, a.recBytes, (long long*)(sb + oSizes),
+                                                                  (long long*)(sb + oOffs), dWbOff, S, C, hdrB, (int)nCh,
+                                                                  d_out, out_capacity, (long long*)(sb + oSOff));
+    k_headers<<<S, 64, 0, st>>>(dTmpl, hdrB, dHdr, (long long*)(sb + oSOff), S, d_out, out_capacity);
+    PAC_CHECK(cudaGetLastError());
+    PAC_CHECK(cudaMemcpyAsync(hOff, sb + oSOff, (S + 1) * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    PAC_CHECK(cudaMemcpyAsync(hHdr, sb + oErr, sizeof(int), cudaMemcpyDeviceToHost, st));
+    PAC_CHECK(cudaStreamSynchronize(st));
+    memcpy(h_stream_off, hOff, (S + 1) * sizeof(long long));
+    if (h_err) *h_err = hHdr[0];
+    if (hOff[S] > out_capacity) return PAC_ERR_ARG;
+    return hHdr[0] ? PAC_ERR_SOFT : 0;
+}

@@ -212,6 +212,9 @@ static int make_pvq(pac_ctx* c) {
     off[PAC_PVQ_LMAX + 1] = (int)all.size();
     for (int L = 0; L < 4; ++L) off[L] = 0;
     int rc;
+    std::vector<double> lg(PAC_PVQ_LMAX + 1, 0.0);
+    for (int L = 1; L <= PAC_PVQ_LMAX; ++L) lg[L] = (double)log2l((long double)L);
+    if ((rc = upload(c, lg, &c->host.log2tab))) return rc;
     if ((rc = upload(c, all, &c->host.pvqN))) return rc;
     return upload(c, off, &c->host.pvqRowOff);
 }

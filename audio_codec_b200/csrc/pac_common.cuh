@@ -67,6 +67,7 @@ struct PacDev {
     // entry exceeding 2^32 (inclusive); rows 0..3 are closed-form and empty here.
     const unsigned long long* pvqN;
     const int* pvqRowOff;      // [PAC_PVQ_LMAX+2]
+    const double* log2tab;     // [PAC_PVQ_LMAX+1] log2(L) (entry 0 unused)
     // SBR decode: response of gaussian_filter1d(sigma=200, reflect) to unit impulses
     const double* sbrGauss;    // [nOmitted][2*(1024-cutoff)] (only first half used)
     int sbrNOmitted;

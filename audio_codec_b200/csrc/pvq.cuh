@@ -1,0 +1,249 @@
+// Gain-shape vector quantiser, encode side: mu-law gain + pyramid VQ shape with
+// the recursive mid/side split flattened onto an explicit stack.  One warp per
+// scale-factor band.  Functional spec: coder/gain_shape_quantize.py:30-124 and
+// :249-403, :476-512 (pvq_search, pvq_codebook_size, encode_pvq_vector,
+// pvq_compute_k_for_R, gain_shape_alloc, bit_allocation_ms, split_band_encode,
+// quantize_gain_shape).
+#pragma once
+#include "quant.cuh"
+
+#define PVQ_SPLIT_BITS 32
+#define PVQ_ERR_FIELD_TOO_WIDE 1   // a theta field wider than 64 bits
+#define PVQ_ERR_DEGENERATE 2       // L<=1 leaf with bits, or an all-zero shape (undefined in the reference)
+#define PVQ_ERR_STACK 4
+
+struct PvqTab {
+    const unsigned long long* N;
+    const int* off;
+    const double* log2tab;   // log2(L), L <= PAC_PVQ_LMAX
+};
+
+// N(l,k): rows 0..3 closed form, others from the table; entries past a row's end
+// are "more than 2^32".
+__device__ __forceinline__ unsigned long long pvq_N(const PvqTab& t, int l, long long k) {
+    if (k <= 0) return 1ull;
+    if (l <= 0) return 0ull;
+    if (l == 1) return 2ull;
+    if (l == 2) return 4ull * (unsigned long long)k;
+    if (l == 3) return 4ull * (unsigned long long)k * (unsigned long long)k + 2ull;
+    int o = t.off[l], len = t.off[l + 1] - o;
+    if (k >= len) return 1ull << 40;
+    return t.N[o + k];
+}
+
+// pvq_compute_k_for_R: largest K with N(L,K) <= 2^bits, and the field width
+// ceil(log2(N(L,K) + eps)) -- which is 1 (not 0) for N == 1.  bits <= 32.
+__device__ __forceinline__ void pvq_k_for_bits(const PvqTab& t, int L, int bits, long long* K, int* used, int* err) {
+    unsigned long long lim = 1ull << bits;
+    long long k = 0;
+    if (L <= 1) {
+        if (bits >= 1) *err |= PVQ_ERR_DEGENERATE;      // the reference never terminates here
+        k = 0;
+    } else if (L == 2) {
+        k = (long long)(lim / 4ull);
+    } else if (L == 3) {
+        if (lim >= 6ull) {
+            unsigned long long q = (lim - 2ull) / 4ull;
+            long long r = (long long)sqrt((double)q);
+            while ((unsigned long long)(r + 1) * (unsigned long long)(r + 1) <= q) ++r;
+            while ((unsigned long long)r * (unsigned long long)r > q) --r;
+            k = r;
+        }
+    } else {
+        int o = t.off[L], len = t.off[L + 1] - o;       // row is ascending; last entry > 2^32
+        int lo = 0, hi = len;                            // first index with N > lim
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (t.N[o + mid] > lim) hi = mid; else lo = mid + 1;
+        }
+        k = lo - 1;
+    }
+    unsigned long long n = pvq_N(t, L, k);
+    *K = k;
+    *used = n <= 1ull ? 1 : 64 - __clzll((long long)(n - 1ull));
+}
+
+// gain_shape_alloc(R, L, 0): coder/gain_shape_quantize.py:57-62
+__device__ __forceinline__ void gs_alloc(const PvqTab& t, int R, int L, int* rg, int* rs) {
+    double g = floor((double)R / (double)L + 0.5 * t.log2tab[L]);
+    *rg = (int)g;
+    double s = (double)R - g;
+    *rs = s > 0.0 ? (int)s : 0;
+}
+
+// bit_allocation_ms: coder/gain_shape_quantize.py:302-312
+__device__ __forceinline__ void ms_alloc(int aMs, double theta, int len, int* aMid, int* aSide) {
+    long long m = 0;
+    if (theta != 0.0) {
+        double v = floor(((double)aMs - (double)(len - 1) * log2(tan(fabs(theta)) + PAC_EPS)) / 2.0);
+        m = v > 1e15 ? (long long)1e15 : (v < -1e15 ? (long long)-1e15 : (long long)v);
+    }
+    if (m < 0) m = 0;
+    if (m > aMs) m = aMs;
+    *aMid = (int)m;
+    *aSide = aMs - (int)m > 0 ? aMs - (int)m : 0;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// quantize_pvq on one warp: x = vec[0..n) (unit L2 norm), residual scratch res[0..n),
+// pulse magnitudes y[0..n).  Returns the Fischer index; *used = field width.
+__device__ __forceinline__ unsigned long long warp_quantize_pvq(const PvqTab& t, const double* vec, double* res,
+                                                                int* y, int n, int bits, int* used, int* err) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    long long K;
+    pvq_k_for_bits(t, n, bits, &K, used, err);
+    if (K == 0) return 0ull;
+    // pvq_search (coder/gain_shape_quantize.py:41-54)
+    double l1 = 0.0;
+    for (int i = lane; i < n; i += 32) l1 += fabs(vec[i]);
+    l1 = warp_sum(l1);
+    if (l1 == 0.0) {
+        *err |= PVQ_ERR_DEGENERATE;
+        return 0ull;
+    }
+    double ps = 0.0;
+    for (int i = lane; i < n; i += 32) {
+        double xh = fabs(((double)K * vec[i]) / l1);
+        double p = floor(xh);
+        res[i] = xh - p;
+        y[i] = (int)p;
+        ps += p;
+    }
+    ps = warp_sum(ps);
+    __syncwarp();
+    long long rem = K - (long long)ps;
+    for (; rem > 0; --rem) {
+        double bv = -1e300;
+        int bi = 0x7fffffff;
+        for (int i = lane; i < n; i += 32) {
+            double r = res[i];
+            if (r > bv) { bv = r; bi = i; }           // strided: first (lowest) index wins per lane
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            double ov = __shfl_xor_sync(FULL, bv, o);
+            int oi = __shfl_xor_sync(FULL, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) {
+            res[bi] -= 1.0;
+            y[bi] += 1;
+        }
+        __syncwarp();
+    }
+    // encode_pvq_vector (coder/gain_shape_quantize.py:105-124), lanes over elements
+    unsigned long long acc = 0ull;
+    long long carry = 0;                               // pulses consumed before this chunk
+    for (int base = 0; base < n; base += 32) {
+        int i = base + lane;
+        int a = i < n ? y[i] : 0;
+        int inc = a;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += v;
+        }
+        long long k = K - carry - (inc - a);           // pulses left when element i is reached
+        if (a > 0) {
+            int l = n - i;
+            bool neg = vec[i] < 0.0;
+            unsigned long long c = pvq_N(t, l - 1, k);
+            for (int j = 1; j < a; ++j) c += 2ull * pvq_N(t, l - 1, k - j);
+            if (neg) c += pvq_N(t, l - 1, k - a);
+            acc += c;
+        }
+        carry += __shfl_sync(FULL, inc, 31);
+    }
+    return warp_sum_u64(acc);
+}
+
+struct PvqNode { short off, cap, n, buf; int bits; };
+
+// quantize_gain_shape for one band on one warp.
+//   x[0..L)   band lines (shared, read only)
+//   wsA/wsB   double workspaces, this band's region of capacity cap = pow2 >= L
+//   yws       int workspace, same region
+//   out       bit writer positioned at this band's private bit buffer
+// Returns the number of bits written (0: all-zero band, caller zeroes bitAlloc).
+__device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const double* x, int L, int R, double* wsA,
+                                                        double* wsB, int* yws, int cap, BitW& out, int* err) {
+    const int lane = threadIdx.x & 31;
+    int bg, bs;
+    gs_alloc(t, R, L, &bg, &bs);
+    double ss = 0.0;
+    for (int i = lane; i < L; i += 32) ss += x[i] * x[i];
+    double gain = sqrt(warp_sum(ss));
+    if (gain == 0.0) return 0;
+    int total = 0;
+    if (bs != 0) {
+        for (int i = lane; i < L; i += 32) wsA[i] = x[i] / gain;
+        __syncwarp();
+        PvqNode st[24];
+        int sp = 0;
+        st[sp++] = {0, (short)cap, (short)L, 0, bs};
+        int used = 0;
+        while (sp > 0) {
+            PvqNode nd = st[--sp];
+            double* cur = (nd.buf ? wsB : wsA) + nd.off;
+            double* oth = (nd.buf ? wsA : wsB) + nd.off;
+            if (nd.bits <= PVQ_SPLIT_BITS) {
+                int w;
+                unsigned long long idx = warp_quantize_pvq(t, cur, oth, yws + nd.off, nd.n, nd.bits, &w, err);
+                if (lane == 0) bw_put(out, idx, w);
+                used += w;
+                continue;
+            }
+            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+            double sm = 0.0, sd = 0.0;
+            for (int i = lane; i < half; i += 32) {
+                double l = i < mid ? cur[i] : 0.0;       // odd n: the LEFT half is zero padded at its end
+                double r = cur[mid + i];
+                double M = (l + r) / 2.0, S = (l - r) / 2.0;
+                oth[i] = M;
+                oth[hc + i] = S;
+                sm += M * M;
+                sd += S * S;
+            }
+            double nm = sqrt(warp_sum(sm)), ns = sqrt(warp_sum(sd));
+            __syncwarp();
+            for (int i = lane; i < half; i += 32) {
+                if (nm != 0.0) oth[i] = oth[i] / nm;
+                if (ns != 0.0) oth[hc + i] = oth[hc + i] / ns;
+            }
+            __syncwarp();
+            double theta = nm == 0.0 ? 0.0 : atan(ns / nm);
+            int aT, aMs, aMid, aSide;
+            gs_alloc(t, nd.bits, half, &aT, &aMs);
+            const double hp = 1.5707963267948966;        // np.pi / 2
+            if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+            unsigned long long ti = quantize_uniform(theta / hp, aT);
+            double tq = dequantize_uniform(ti, aT) * hp;
+            ms_alloc(aMs, tq, half, &aMid, &aSide);
+            if (lane == 0) bw_put(out, ti, aT);
+            used += aT;
+            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
+            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide};
+            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid};
+        }
+        bg += bs - used;
+        total = used;
+    }
+    double g = log(1.0 + 255.0 * (gain / (double)L)) / log(256.0);      // mu_law_fn
+    if (bg < 0) bg = 0;
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    unsigned long long gi = quantize_uniform(g, bg);
+    if (lane == 0) bw_put(out, gi, bg);
+    __syncwarp();
+    return total + bg;
+}

@@ -65,6 +65,27 @@ int pac_mdct_forward(pac_ctx* ctx, int dtype, const void* d_x, long long row_str
 int pac_imdct_ola(pac_ctx* ctx, int dtype, const void* d_coefs, int n_rows, int n_frames, int N,
                   int window, void* d_y, long long row_stride, void* stream);
 
+/* ---- whole-stream encode: replaces the "Encode" leg of pacfile.encode_decode_test
+ * (coder/pacfile.py:674-756): PCMFile.ReadDataBlock's int16 -> float mapping
+ * (coder/pcmfile.py:89-98), parTransientDetect (coder/detect_transients.py:5-23),
+ * PACFile.WriteDataBlock (coder/pacfile.py:449-610) -> codec.Encode / Encode_SBR
+ * (coder/codec.py:225-555: window, MDCT, ScaleFactor, CalcSMRs, BitAlloc[_SBR],
+ * quantize_gain_shape | ScaleFactor+vMantissa), PackedBits.WriteBits, the length
+ * prefixes, WriteFileHeader and Close().
+ *
+ * d_pcm: int16 planar, block-padded: stream s owns h_nblocks[s] blocks of 1024
+ * samples per channel at element offset (sum_{t<s} nblocks[t] * C + c * nblocks[s]) * 1024.
+ * h_hdr_samples[s]: sample count the header's numSamples is derived from.
+ * d_out: caller buffer of out_capacity bytes (>= pac_encode_bound()); stream s'
+ * .pac image is d_out[h_stream_off[s] .. h_stream_off[s+1]).  *h_err receives
+ * the OR of per-frame soft-error flags (inputs whose behaviour is undefined in
+ * the reference); the call then returns PAC_ERR_SOFT.  Synchronises `stream`. */
+int pac_header_bytes(const pac_ctx* ctx);
+long long pac_encode_bound(const pac_ctx* ctx, const int* h_nblocks, int n_streams);
+int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h_nblocks, const int* h_hdr_samples,
+                       int n_streams, unsigned char* d_out, long long out_capacity,
+                       long long* h_stream_off, int* h_err, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
