@@ -43,6 +43,8 @@ def _load():
         "pac_header_bytes": (i, [vp]),
         "pac_encode_bound": (ll, [vp, C.POINTER(i), i]),
         "pac_encode_streams": (i, [vp, vp, C.POINTER(i), C.POINTER(i), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
+        "pac_decode_plan": (i, [vp, vp, C.POINTER(ll), i, C.POINTER(ll), vp]),
+        "pac_decode_streams": (i, [vp, vp, C.POINTER(ll), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -53,7 +55,7 @@ def _load():
 
 lib = _load()
 EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola",
-           "pac_header_bytes", "pac_encode_bound", "pac_encode_streams"]
+           "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams"]
 
 
 def check(rc):

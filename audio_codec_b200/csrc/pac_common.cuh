@@ -16,6 +16,7 @@
 #define PAC_HALF_SHORT 128
 #define PAC_SUBFRAMES 8
 #define PAC_PVQ_LMAX 1024
+#define PAC_EPS 2.220446049250313e-16   // np.finfo(float).eps
 
 // window shapes (coder/window.py:14-92, selected by coder/codec.py:30-44)
 enum { PAC_WIN_SINE = 0, PAC_WIN_START = 1, PAC_WIN_STOP = 2, PAC_WIN_STARTSTOP = 3,

@@ -1,0 +1,143 @@
+// Gain-shape vector dequantiser: parses a band's fields straight from the
+// bitstream (field widths depend on the theta values just read), one warp per
+// band.  Functional spec: coder/gain_shape_quantize.py:127-186 (decoder.step_*),
+// :263-272 (dequantize_pvq), :406-473 (split_band_decode), :515-538
+// (dequantize_gain_shape).
+#pragma once
+#include "pvq.cuh"
+
+// Fischer index -> pulse vector (the reference's recursive step_1..step_5 walk).
+// Serial; run by one lane.  x[0..L) receives signed pulse counts as doubles.
+__device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b, int L, long long K, double* x,
+                                           int* err) {
+    for (int i = 0; i < L; ++i) x[i] = 0.0;
+    unsigned long long xb = 0ull;
+    long long k = K;
+    int l = L, i = 0;
+    int guard = 0;
+    while (true) {
+        if (++guard > 100000 || i >= L) { *err |= PVQ_ERR_DEGENERATE; return; }
+        if (b == xb) {                                    // step 1 (+ step 5)
+            x[i] = 0.0;
+            if (k > 0) x[L - 1] = (double)k;
+            return;
+        }
+        unsigned long long n0 = pvq_N(t, l - 1, k);       // step 2
+        long long xi = 0;
+        if (b >= xb + n0) {
+            xb += n0;
+            long long j = 1;
+            bool found = false;
+            while (true) {                                // step 3
+                if (j > k) j = k;
+                unsigned long long nj = pvq_N(t, l - 1, k - j);
+                if (b < xb + 2ull * nj) {
+                    xi = (b >= xb + nj) ? -j : j;
+                    found = true;
+                    break;
+                }
+                xb += 2ull * nj;
+                if (j < k) ++j; else break;
+            }
+            if (!found) continue;                         // reference jumps back to step 1
+        }
+        x[i] = (double)xi;                                // step 4
+        k -= xi < 0 ? -xi : xi;
+        l -= 1;
+        i += 1;
+        if (k <= 0) return;
+    }
+}
+
+struct DecNode { short off, cap, n, buf; int bits; double theta; short state, root; };
+
+// dequantize_gain_shape for one band on one warp.  Reads exactly R bits from br
+// (all lanes hold the same cursor).  out[0..L) <- gain * shape.
+__device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR br, int R, int L, double* wsA,
+                                                           double* wsB, int cap, double* out, int* err) {
+    const int lane = threadIdx.x & 31;
+    int bg, bs;
+    gs_alloc(t, R, L, &bg, &bs);
+    if (bs != 0) {
+        DecNode st[24];
+        int sp = 0;
+        st[sp++] = {0, (short)cap, (short)L, 0, bs, 0.0, 0, 1};
+        int used = 0;
+        while (sp > 0) {
+            DecNode& nd = st[sp - 1];
+            double* cur = (nd.buf ? wsB : wsA) + nd.off;
+            double* oth = (nd.buf ? wsA : wsB) + nd.off;
+            if (nd.bits <= PVQ_SPLIT_BITS) {              // leaf
+                long long K;
+                int w;
+                pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+                unsigned long long idx = br_get(br, w);
+                used += w;
+                if (lane == 0) pvq_vector(t, idx, nd.n, K, cur, err);
+                __syncwarp();
+                const int reps = nd.root ? 2 : 1;         // a root leaf is normalised twice (:214-218)
+                for (int r = 0; r < reps; ++r) {
+                    double ss = 0.0;
+                    for (int i = lane; i < nd.n; i += 32) ss += cur[i] * cur[i];
+                    double nr = sqrt(warp_sum(ss));
+                    if (nr != 0.0)
+                        for (int i = lane; i < nd.n; i += 32) cur[i] = cur[i] / nr;
+                    __syncwarp();
+                }
+                --sp;
+                continue;
+            }
+            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+            if (nd.state == 0) {                          // first visit: theta, then children
+                int aT, aMs, aMid, aSide;
+                gs_alloc(t, nd.bits, half, &aT, &aMs);
+                if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+                unsigned long long ti = br_get(br, aT);
+                used += aT;
+                nd.theta = dequantize_uniform(ti, aT) * 1.5707963267948966;
+                ms_alloc(aMs, nd.theta, half, &aMid, &aSide);
+                nd.state = 1;
+                for (int i = lane; i < half; i += 32) {   // children that get no bits stay zero
+                    if (aMid <= 0) oth[i] = 0.0;
+                    if (aSide <= 0) oth[hc + i] = 0.0;
+                }
+                __syncwarp();
+                if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; return; }
+                const short off = nd.off, buf = nd.buf;   // nd is invalidated by the pushes below
+                if (aSide > 0) st[sp++] = {(short)(off + hc), (short)hc, (short)half, (short)(1 - buf), aSide, 0.0, 0, 0};
+                if (aMid > 0) st[sp++] = {off, (short)hc, (short)half, (short)(1 - buf), aMid, 0.0, 0, 0};
+                continue;
+            }
+            // children done: recombine (coder/gain_shape_quantize.py:449-463)
+            const double ct = cos(nd.theta), sn = sin(nd.theta), r2 = sqrt(2.0);
+            double ss = 0.0;
+            for (int i = lane; i < half; i += 32) {
+                double m = oth[i], s = oth[hc + i];
+                double l = (m * ct + s * sn) / r2;
+                double r = (m * ct - s * sn) / r2;
+                if (i < mid) { cur[i] = l; ss += l * l; }  // odd n: the padded last element of left is dropped
+                cur[mid + i] = r;
+                ss += r * r;
+            }
+            double nr = sqrt(warp_sum(ss));
+            __syncwarp();
+            if (nr != 0.0)
+                for (int i = lane; i < n; i += 32) cur[i] = cur[i] / nr;
+            __syncwarp();
+            --sp;
+        }
+        bg += bs - used;
+    } else {
+        for (int i = lane; i < L; i += 32) wsA[i] = 1.0;
+        __syncwarp();
+    }
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    if (bg < 0) bg = 0;
+    unsigned long long gi = br_get(br, bg);
+    double gq = dequantize_uniform(gi, bg);
+    // inv_mu_law_fn: sign(y)/mu * ((1+mu)^|y| - 1)
+    double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
+    double gain = sg / 255.0 * (pow(256.0, fabs(gq)) - 1.0) * (double)L;
+    for (int i = lane; i < L; i += 32) out[i] = gain * wsA[i];
+    __syncwarp();
+}

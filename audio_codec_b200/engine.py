@@ -58,3 +58,56 @@ def encode_streams(ctx, pcm_list, hdr_samples=None):
                             "undefined in the reference)")
     host = d_out[:int(off[-1])].cpu().numpy().tobytes()
     return [host[int(off[s]):int(off[s + 1])] for s in range(len(pcm_list))]
+
+
+def parse_header(buf):
+    """coder/pacfile.py:136-151 -> dict of the header fields."""
+    import struct
+    if buf[:4] != b"PAC ":
+        raise RuntimeError("Tried to read a non-PAC file into a PACFile object")
+    fs, C_, ns, nl, nsb, nmsb, sbr, vq = struct.unpack_from("<LHLLHHHH", buf, 4)
+    nb = struct.unpack_from("<L", buf, 26)[0]
+    lines = struct.unpack_from("<%dH" % nb, buf, 30)
+    return dict(sample_rate=fs, n_channels=C_, num_samples=ns, n_mdct_lines=nl, n_scale_bits=nsb,
+                n_mant_size_bits=nmsb, use_sbr=bool(sbr), use_vq=bool(vq), n_lines=lines)
+
+
+def context_for_header(h):
+    ctx = _lib.default_context(h["sample_rate"], n_channels=h["n_channels"], use_vq=h["use_vq"],
+                               use_sbr=h["use_sbr"], n_scale_bits=h["n_scale_bits"],
+                               n_mant_size_bits=h["n_mant_size_bits"])
+    nl, _ = ctx.bands()
+    if tuple(int(v) for v in nl) != tuple(h["n_lines"]) or h["n_mdct_lines"] != 1024:
+        raise _lib.PacError("unsupported band layout in .pac header")
+    return ctx
+
+
+def decode_device(ctx, d_pac, stream_off, d_pcm=None):
+    """d_pac: uint8 CUDA tensor holding the streams back to back.  Returns
+    (d_pcm int16, pcm_off[S+1] in samples, err)."""
+    S = len(stream_off) - 1
+    so = (C.c_longlong * (S + 1))(*[int(v) for v in stream_off])
+    po = (C.c_longlong * (S + 1))()
+    if d_pcm is None:
+        _lib.check(_lib.lib.pac_decode_plan(ctx.h, C.c_void_p(d_pac.data_ptr()), so, S, po, _lib.stream_ptr()))
+        d_pcm = torch.empty(int(po[S]), dtype=torch.int16, device=d_pac.device)
+    err = C.c_int(0)
+    rc = _lib.lib.pac_decode_streams(ctx.h, C.c_void_p(d_pac.data_ptr()), so, S, C.c_void_p(d_pcm.data_ptr()),
+                                     d_pcm.numel(), po, C.byref(err), _lib.stream_ptr())
+    if rc != 0 and rc != -4:
+        _lib.check(rc)
+    return d_pcm, np.array(po[:]), err.value
+
+
+def decode_streams(pac_list):
+    """Host convenience: list of .pac bytes (same configuration) -> list of int16 [C, n]."""
+    h = parse_header(pac_list[0])
+    ctx = context_for_header(h)
+    off = np.concatenate([[0], np.cumsum([len(b) for b in pac_list])])
+    d_pac = torch.from_numpy(np.frombuffer(b"".join(pac_list), dtype=np.uint8).copy()).cuda()
+    d_pcm, po, err = decode_device(ctx, d_pac, off)
+    if err:
+        raise _lib.PacError(f"soft error flags {err:#x} while decoding")
+    pcm = d_pcm.cpu().numpy()
+    Cn = h["n_channels"]
+    return [pcm[int(po[s]):int(po[s + 1])].reshape(Cn, -1) for s in range(len(pac_list))]

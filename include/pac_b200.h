@@ -86,6 +86,25 @@ int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h_nblocks, c
                        int n_streams, unsigned char* d_out, long long out_capacity,
                        long long* h_stream_off, int* h_err, void* stream);
 
+/* ---- whole-stream decode: replaces the "Decode" leg of pacfile.encode_decode_test:
+ * PACFile.ReadDataBlock / getDecodedBlock (coder/pacfile.py:177-298: length-prefix
+ * walk, flag bits, scale / bit-allocation fields), codec.Decode / Decode_SBR
+ * (coder/codec.py:47-222: dequantize_gain_shape | vDequantize, SBR envelope +
+ * transposition, IMDCT, synthesis window), the short-block and block overlap-add,
+ * and PCMFile.WriteDataBlock's 16-bit quantiser (coder/pcmfile.py:118-147).
+ *
+ * d_pac: the .pac images back to back, stream s at [h_stream_off[s], h_stream_off[s+1]);
+ * every stream must have been coded with this context's configuration (header
+ * fields are the caller's to check).  Output: int16 planar; stream s channel c is
+ * d_pcm[h_pcm_off[s] + c*n_s .. + n_s), n_s = (h_pcm_off[s+1]-h_pcm_off[s])/C samples
+ * (all written blocks plus the final overlap flush, i.e. what the reference's WAV
+ * writer receives).  pac_decode_plan only walks the length prefixes and fills
+ * h_pcm_off so the caller can size d_pcm.  Both synchronise `stream`. */
+int pac_decode_plan(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off, int n_streams,
+                    long long* h_pcm_off, void* stream);
+int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off, int n_streams,
+                       short* d_pcm, long long pcm_capacity, long long* h_pcm_off, int* h_err, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
