@@ -43,6 +43,9 @@ def _load():
         "pac_header_bytes": (i, [vp]),
         "pac_encode_bound": (ll, [vp, C.POINTER(i), i]),
         "pac_encode_streams": (i, [vp, vp, C.POINTER(i), C.POINTER(i), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
+        "pac_encode_host": (i, [vp, vp, C.POINTER(i), C.POINTER(i), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
+        "pac_decode_host": (i, [vp, vp, C.POINTER(ll), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
+        "pac_last_kernel_ms": (i, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "pac_decode_plan": (i, [vp, vp, C.POINTER(ll), i, C.POINTER(ll), vp]),
         "pac_decode_streams": (i, [vp, vp, C.POINTER(ll), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
     }
@@ -55,7 +58,8 @@ def _load():
 
 lib = _load()
 EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola",
-           "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams"]
+           "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams", "pac_last_kernel_ms",
+           "pac_encode_host", "pac_decode_host"]
 
 
 def check(rc):
@@ -88,6 +92,11 @@ class Context:
         o = (C.c_int * 32)()
         nb = check(lib.pac_get_bands(self.h, int(short), n, o))
         return np.array(n[:nb]), np.array(o[:nb])
+
+    def last_kernel_ms(self):
+        e, d = C.c_float(), C.c_float()
+        check(lib.pac_last_kernel_ms(self.h, C.byref(e), C.byref(d)))
+        return e.value, d.value
 
     def close(self):
         if getattr(self, "h", None):

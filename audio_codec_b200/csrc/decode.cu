@@ -365,7 +365,10 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
         size_t smem = (1024 + 2048 * 3) * sizeof(double) + (32 * 2 + 34 * 2 + 16) * sizeof(int) + DEC_REC_MAX;
         PAC_CHECK(cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaEventRecord(ctx->ev[2], st);
         k_decode<<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);
+        cudaEventRecord(ctx->ev[3], st);
+        ctx->evValid[1] = 1;
         PAC_CHECK(cudaGetLastError());
     }
     const long long nOut = pcmOff[S] / 1024;

@@ -592,7 +592,10 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     size_t smem = (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
                   (REC_WORDS + BAND_WORDS) * sizeof(unsigned) + (32 * 4 + 34 * 2 + 16) * sizeof(int);
     PAC_CHECK(cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaEventRecord(ctx->ev[0], st);
     k_encode<<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
+    cudaEventRecord(ctx->ev[1], st);
+    ctx->evValid[0] = 1;
     PAC_CHECK(cudaGetLastError());
     k_sizes<<<(unsigned)((nCh + 255) / 256), 256, 0, st>>>(a.recBytes, a.zeroSub, dWbOff, S, C, hdrB, (int)nCh,
                                                            (long long*)(sb + oSizes));

@@ -273,6 +273,10 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     c->scratchBytes = 0;
     c->pinned = nullptr;
     c->pinnedBytes = 0;
+    for (int i = 0; i < 4; ++i) cudaEventCreate(&c->ev[i]);
+    c->evValid[0] = c->evValid[1] = 0;
+    c->io[0] = c->io[1] = nullptr;
+    c->ioBytes[0] = c->ioBytes[1] = 0;
     memset(&c->host, 0, sizeof(c->host));
     PacDev& h = c->host;
     h.fs = cfg->sample_rate;
@@ -316,6 +320,8 @@ extern "C" void pac_destroy(pac_ctx* c) {
     for (void* p : c->allocs) cudaFree(p);
     if (c->scratch) cudaFree(c->scratch);
     if (c->pinned) cudaFreeHost(c->pinned);
+    for (int i = 0; i < 2; ++i) if (c->io[i]) cudaFree(c->io[i]);
+    for (int i = 0; i < 4; ++i) cudaEventDestroy(c->ev[i]);
     delete c;
 }
 
@@ -328,6 +334,18 @@ int pac_scratch(pac_ctx* c, size_t bytes, void** out) {
         c->scratchBytes = bytes;
     }
     *out = c->scratch;
+    return 0;
+}
+
+int pac_io(pac_ctx* c, int which, size_t bytes, void** out) {
+    if (bytes > c->ioBytes[which]) {
+        if (c->io[which]) cudaFree(c->io[which]);
+        c->io[which] = nullptr;
+        c->ioBytes[which] = 0;
+        if (cudaMalloc(&c->io[which], bytes + 256) != cudaSuccess) return PAC_ERR_ALLOC;
+        c->ioBytes[which] = bytes;
+    }
+    *out = c->io[which];
     return 0;
 }
 
@@ -364,4 +382,13 @@ extern "C" int pac_get_bands(const pac_ctx* c, int which, int* n_lines, int* omi
         if (omitted) omitted[k] = b.omitted[k];
     }
     return b.nBands;
+}
+
+// Device time of the dominant kernel of the last pac_encode_streams / pac_decode_streams
+// call on this context (CUDA events recorded on the caller's stream around the launch).
+extern "C" int pac_last_kernel_ms(pac_ctx* c, float* enc_ms, float* dec_ms) {
+    if (!c) return PAC_ERR_ARG;
+    if (enc_ms) { *enc_ms = -1.f; if (c->evValid[0]) cudaEventElapsedTime(enc_ms, c->ev[0], c->ev[1]); }
+    if (dec_ms) { *dec_ms = -1.f; if (c->evValid[1]) cudaEventElapsedTime(dec_ms, c->ev[2], c->ev[3]); }
+    return 0;
 }

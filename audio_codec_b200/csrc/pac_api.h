@@ -15,7 +15,12 @@ struct pac_ctx {
     size_t scratchBytes;
     void* pinned;
     size_t pinnedBytes;
+    void* io[2];         // device staging for the host-buffer entry points
+    size_t ioBytes[2];
+    cudaEvent_t ev[4];   // around k_encode and k_decode, for pac_last_kernel_ms
+    int evValid[2];
 };
 
 int pac_scratch(pac_ctx* ctx, size_t bytes, void** out);
 int pac_pinned(pac_ctx* ctx, size_t bytes, void** out);
+int pac_io(pac_ctx* ctx, int which, size_t bytes, void** out);

@@ -111,3 +111,32 @@ def decode_streams(pac_list):
     pcm = d_pcm.cpu().numpy()
     Cn = h["n_channels"]
     return [pcm[int(po[s]):int(po[s + 1])].reshape(Cn, -1) for s in range(len(pac_list))]
+
+
+def encode_host(ctx, h_pcm, n_blocks, hdr_samples, h_out):
+    """Host buffers in and out (torch CPU tensors, ideally pinned): int16 PCM in the
+    pack_pcm layout -> .pac bytes in h_out.  Returns (stream_off[S+1], err)."""
+    S = len(n_blocks)
+    nb = (C.c_int * S)(*[int(v) for v in n_blocks])
+    hs = (C.c_int * S)(*[int(v) for v in hdr_samples])
+    off = (C.c_longlong * (S + 1))()
+    err = C.c_int(0)
+    rc = _lib.lib.pac_encode_host(ctx.h, C.c_void_p(h_pcm.data_ptr()), nb, hs, S, C.c_void_p(h_out.data_ptr()),
+                                  h_out.numel(), off, C.byref(err), _lib.stream_ptr())
+    if rc != 0 and rc != -4:
+        _lib.check(rc)
+    return np.array(off[:]), err.value
+
+
+def decode_host(ctx, h_pac, stream_off, h_pcm):
+    """Host buffers in and out: .pac bytes -> int16 PCM.  Returns (pcm_off[S+1], err)."""
+    S = len(stream_off) - 1
+    so = (C.c_longlong * (S + 1))(*[int(v) for v in stream_off])
+    po = (C.c_longlong * (S + 1))()
+    err = C.c_int(0)
+    rc = _lib.lib.pac_decode_host(ctx.h, C.c_void_p(h_pac.data_ptr()), so, S,
+                                  C.c_void_p(h_pcm.data_ptr()) if h_pcm is not None else None,
+                                  h_pcm.numel() if h_pcm is not None else 0, po, C.byref(err), _lib.stream_ptr())
+    if rc != 0 and rc != -4:
+        _lib.check(rc)
+    return np.array(po[:]), err.value

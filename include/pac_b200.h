@@ -105,6 +105,21 @@ int pac_decode_plan(pac_ctx* ctx, const unsigned char* d_pac, const long long* h
 int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off, int n_streams,
                        short* d_pcm, long long pcm_capacity, long long* h_pcm_off, int* h_err, void* stream);
 
+/* Host-buffer forms of the two calls above (ordinary or pinned host memory in
+ * and out; H2D copy, device pipeline, D2H copy on `stream`).  This is what a host
+ * driver standing in for pacfile.encode_decode_test calls.  pac_decode_host with
+ * h_pcm == NULL only fills h_pcm_off. */
+int pac_encode_host(pac_ctx* ctx, const short* h_pcm, const int* h_nblocks, const int* h_hdr_samples,
+                    int n_streams, unsigned char* h_out, long long out_capacity, long long* h_stream_off,
+                    int* h_err, void* stream);
+int pac_decode_host(pac_ctx* ctx, const unsigned char* h_pac, const long long* h_stream_off, int n_streams,
+                    short* h_pcm, long long pcm_capacity, long long* h_pcm_off, int* h_err, void* stream);
+
+/* Measurement aid (no reference counterpart): device milliseconds of the dominant
+ * kernel (k_encode / k_decode) of the last encode / decode call on this context,
+ * from CUDA events recorded on the caller's stream; -1 if none yet. */
+int pac_last_kernel_ms(pac_ctx* ctx, float* enc_ms, float* dec_ms);
+
 #ifdef __cplusplus
 }
 #endif
