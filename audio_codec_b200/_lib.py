@@ -13,7 +13,8 @@ _PKG = Path(__file__).resolve().parent
 _LIB_PATH = _PKG / "libpac_b200.so"
 
 F32, F64 = 0, 1
-W_SINE, W_START, W_STOP, W_STARTSTOP, W_KAISER, W_NONE = range(6)
+W_SINE, W_START, W_STOP, W_STARTSTOP, W_KAISER, W_NONE, W_HANN = range(7)
+PSY_SPL, PSY_INTENSITY, PSY_BARK, PSY_THRESH = range(4)
 
 
 class PacConfig(C.Structure):
@@ -33,6 +34,7 @@ def _load():
             "(nvcc, sm_100a). There is no CPU fallback.")
     lib = C.CDLL(str(_LIB_PATH))
     vp, ll, i, d = C.c_void_p, C.c_longlong, C.c_int, C.c_double
+    pi = C.POINTER(C.c_int)
     sig = {
         "pac_create": (i, [i, C.POINTER(PacConfig), C.POINTER(vp)]),
         "pac_destroy": (None, [vp]),
@@ -48,6 +50,26 @@ def _load():
         "pac_last_kernel_ms": (i, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "pac_decode_plan": (i, [vp, vp, C.POINTER(ll), i, C.POINTER(ll), vp]),
         "pac_decode_streams": (i, [vp, vp, C.POINTER(ll), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
+        # per-function ops
+        "pac_window": (i, [vp, i, vp, ll, i, i, i, d, vp, vp]),
+        "pac_transient_detect": (i, [vp, vp, ll, i, i, d, vp, vp]),
+        "pac_calc_smr": (i, [vp, vp, vp, vp, ll, i, i, pi, pi, vp, vp, vp]),
+        "pac_psy_map": (i, [vp, i, vp, ll, vp, vp]),
+        "pac_bit_alloc": (i, [vp, vp, i, i, pi, vp, ll, vp, vp]),
+        "pac_quantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
+        "pac_dequantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
+        "pac_scale_factor": (i, [vp, vp, ll, i, i, vp, vp]),
+        "pac_mantissa": (i, [vp, vp, ll, i, i, i, vp, vp]),
+        "pac_dequantize": (i, [vp, i, vp, ll, i, i, vp, vp]),
+        "pac_gain_shape_quantize": (i, [vp, vp, i, ll, vp, i, vp, vp, vp, i, pi, vp]),
+        "pac_gain_shape_dequantize": (i, [vp, vp, ll, vp, vp, i, ll, vp, vp, pi, vp]),
+        "pac_pack_bits": (i, [vp, vp, vp, vp, i, ll, i, vp, pi, vp]),
+        "pac_unpack_bits": (i, [vp, vp, i, vp, vp, vp, i, ll, vp, vp]),
+        "pac_record_stride": (i, []),
+        "pac_encode_blocks": (i, [vp, vp, vp, ll, vp, vp, vp, pi, vp]),
+        "pac_encode_frames": (i, [vp, vp, i, vp, i, ll, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, pi, vp]),
+        "pac_decode_blocks": (i, [vp, vp, i, vp, ll, vp, pi, vp]),
+        "pac_decode_frames": (i, [vp, vp, i, vp, i, vp, ll, vp, vp, pi, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -59,7 +81,11 @@ def _load():
 lib = _load()
 EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola",
            "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams", "pac_last_kernel_ms",
-           "pac_encode_host", "pac_decode_host"]
+           "pac_encode_host", "pac_decode_host",
+           "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_bit_alloc", "pac_quantize_uniform",
+           "pac_dequantize_uniform", "pac_scale_factor", "pac_mantissa", "pac_dequantize", "pac_gain_shape_quantize",
+           "pac_gain_shape_dequantize", "pac_pack_bits", "pac_unpack_bits", "pac_record_stride", "pac_encode_blocks",
+           "pac_encode_frames", "pac_decode_blocks", "pac_decode_frames"]
 
 
 def check(rc):
@@ -68,20 +94,30 @@ def check(rc):
     return rc
 
 
+def check_soft(rc, err):
+    """For calls that report per-item soft errors: PAC_ERR_SOFT raises with the flags."""
+    if rc == -4:
+        raise PacError(f"libpac_b200: soft error flags {err.value:#x} (input whose behaviour is undefined in the "
+                       "reference: degenerate PVQ vector, field wider than 64 bits, or malformed bitstream)")
+    return check(rc)
+
+
 class Context:
     """One per (GPU, configuration).  Mirrors the reference's CodingParams fields
     (coder/pacfile.py:157-174, :699-707)."""
 
     def __init__(self, sample_rate=48000, n_channels=2, rate_kbps=128.0, use_vq=True, use_sbr=None,
-                 n_scale_bits=4, n_mant_size_bits=12, device=None):
+                 n_scale_bits=4, n_mant_size_bits=12, device=None, target_bits_per_sample=None):
         import torch
         if not torch.cuda.is_available():
             raise PacError("no CUDA device: audio_codec_b200 has no CPU path")
         self.device = torch.cuda.current_device() if device is None else int(device)
         if use_sbr is None:
             use_sbr = rate_kbps < 128
+        if target_bits_per_sample is None:
+            target_bits_per_sample = float(rate_kbps) / (sample_rate / 1000)     # coder/pacfile.py:702
         self.cfg = PacConfig(int(sample_rate), int(n_channels), 1024, int(n_scale_bits), int(n_mant_size_bits),
-                             int(bool(use_sbr)), int(bool(use_vq)), float(rate_kbps) / (sample_rate / 1000))
+                             int(bool(use_sbr)), int(bool(use_vq)), float(target_bits_per_sample))
         self.rate_kbps = rate_kbps
         h = C.c_void_p()
         check(lib.pac_create(self.device, C.byref(self.cfg), C.byref(h)))

@@ -9,12 +9,9 @@
 //               (coder/pacfile.py:289-295, coder/pcmfile.py:118-147)
 #include <string.h>
 #include <vector>
-#include "mdct.cuh"
+#include "decode_frame.cuh"
 #include "pac_api.h"
-#include "pvq_dec.cuh"
 
-#define DEC_NT 256
-#define DEC_REC_MAX 4096          // largest channel-block payload accepted (bytes)
 extern "C" int pac_header_bytes(const pac_ctx* ctx);
 
 // pass 0: count channel-blocks; pass 1: record payload offsets (absolute, past the prefix)
@@ -38,160 +35,6 @@ __global__ void k_walk(const unsigned char* __restrict__ buf, const long long* _
         pos += 4 + nb;
     }
     if (counts) counts[s] = n;
-}
-
-struct DecSmem {
-    unsigned char* rec;   // [DEC_REC_MAX] payload bytes
-    double* lines;        // [1024] dequantised MDCT lines of the current frame
-    double* wsA;          // [2048] PVQ workspace A; later FFT buffer (first 1024) + DCT-IV output (last 1024)
-    double* wsB;          // [2048] PVQ workspace B; SBR scratch
-    double* y;            // [2048] windowed time samples of the block (short sub-frames overlap-added)
-    int* ba;              // [32]
-    int* sfb;             // [32]
-    int* bandPos;         // [33] bit position of each band's payload
-    int* capOff;          // [33]
-    int* misc;            // [16]
-};
-
-// Decode one frame of H = N/2 lines whose fields start at bit *bpos of the record;
-// adds its windowed IMDCT into y[yOff .. yOff+N).
-template <int N>
-__device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, long long recBits, int shape, int yOff,
-                             int* err) {
-    constexpr int H = N / 2, Q = N / 4;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const bool isLong = N == PAC_NLONG;
-    const PacBands& bands = isLong ? dev->longBands : dev->shortBands;
-    const int nB = bands.nBands;
-    // (1) frame header: overall scale, bit allocations (+ BFP scale factors): thread 0
-    if (tid == 0) {
-        BitR br = {S.rec, S.misc[3], recBits};
-        S.misc[5] = (int)br_get(br, dev->nScaleBits);
-        bool anyOm = false;
-        if (dev->useVQ) {
-            for (int b = 0; b < nB; ++b) {
-                int v = (int)br_get(br, dev->nMantSizeBits);
-                S.ba[b] = v ? v + 1 : 0;
-            }
-            for (int b = 0; b < nB; ++b) anyOm |= isLong && bands.omitted[b] && S.ba[b] != 0;
-            const bool sbr = isLong && dev->useSBR && anyOm;          // coder/pacfile.py:660-664
-            S.misc[6] = sbr;
-            long long p = br.pos;
-            for (int b = 0; b < nB; ++b) {
-                S.bandPos[b] = (int)p;
-                if (S.ba[b]) p += (long long)S.ba[b] * ((sbr && bands.omitted[b]) ? 1 : bands.nLines[b]);
-            }
-            br.pos = p;
-        } else {
-            S.misc[6] = 0;
-            for (int b = 0; b < nB; ++b) {
-                int v = (int)br_get(br, dev->nMantSizeBits);
-                S.ba[b] = v ? v + 1 : 0;
-                S.sfb[b] = (int)br_get(br, dev->nScaleBits);
-                S.bandPos[b] = (int)br.pos;
-                if (S.ba[b]) br.pos += (long long)S.ba[b] * bands.nLines[b];
-            }
-        }
-        S.misc[3] = (int)br.pos;
-        int c = 0;
-        for (int b = 0; b < nB; ++b) {
-            S.capOff[b] = c;
-            int cap = 1;
-            while (cap < bands.nLines[b]) cap <<= 1;
-            c += cap;
-        }
-        S.capOff[nB] = c;
-        if (br.pos > recBits) atomicOr(err, PVQ_ERR_STACK);
-    }
-    for (int i = tid; i < H; i += DEC_NT) S.lines[i] = 0.0;
-    __syncthreads();
-    const bool sbr = S.misc[6] != 0;
-    const int scale = S.misc[5];
-    // (2) bands in parallel, one warp each
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab};
-    int omPos = dev->sbrCutoff;
-    for (int b = warp; b < nB; b += DEC_NT / 32) {
-        const int bb = S.ba[b];
-        if (!bb) continue;
-        const int lo = bands.lower[b], n = bands.nLines[b];
-        if (dev->useVQ) {
-            BitR br = {S.rec, S.bandPos[b], recBits};
-            int werr = 0;
-            const int cap = S.capOff[b + 1] - S.capOff[b];
-            if (sbr && bands.omitted[b]) {
-                // one envelope value, stored at consecutive lines from the cut-off (coder/codec.py:111-132)
-                int k = 0;
-                for (int q = 0; q < b; ++q) k += bands.omitted[q] ? 1 : 0;
-                warp_dequantize_gain_shape(pt, br, bb, 1, S.wsA + S.capOff[b], S.wsB + S.capOff[b], cap,
-                                           S.lines + omPos + k, &werr);
-            } else {
-                warp_dequantize_gain_shape(pt, br, bb * n, n, S.wsA + S.capOff[b], S.wsB + S.capOff[b], cap,
-                                           S.lines + lo, &werr);
-            }
-            if (werr && lane == 0) atomicOr(err, werr);
-        } else {
-            for (int i = lane; i < n; i += 32) {
-                BitR br = {S.rec, (long long)S.bandPos[b] + (long long)i * bb, recBits};
-                unsigned m = (unsigned)br_get(br, bb);
-                S.lines[lo + i] = dequantize_bfp(S.sfb[b], m, dev->nScaleBits, bb);
-            }
-        }
-    }
-    __syncthreads();
-    // (3) SBR: envelope smoothing, 2:1 transposition of the low band, per-band envelope
-    //     scaling (coder/codec.py:134-194)
-    if (isLong && sbr) {
-        const int cut = dev->sbrCutoff, nLen = H - cut, nOm = dev->sbrNOmitted;
-        double* hi = S.wsB;               // transposed high band [nLen]
-        double* smooth = S.wsB + 1024;    // smoothed envelope [nLen]
-        for (int i = tid; i < nLen; i += DEC_NT) {
-            double e = 0.0;
-            for (int p = 0; p < nOm; ++p) e += S.lines[cut + p] * dev->sbrGauss[(size_t)p * nLen + i];
-            smooth[i] = e;
-            // interp1d('slinear') of the lines at frequency (k+1/2)/2 bins: between line m-1 and m
-            // (k even) or m and m+1 (k odd), k = cut+i, m = k/2; weights are exactly 1/4, 3/4
-            int k = cut + i, m = k >> 1;
-            double v;
-            if ((k & 1) == 0) v = 0.25 * S.lines[m - 1] + 0.75 * S.lines[m];
-            else v = 0.75 * S.lines[m] + 0.25 * S.lines[m + 1];
-            hi[i] = v;
-        }
-        __syncthreads();
-        for (int i = tid; i < nLen; i += DEC_NT) S.lines[cut + i] = hi[i];
-        __syncthreads();
-        for (int b = warp; b < nB; b += DEC_NT / 32) {
-            if (!bands.omitted[b]) continue;
-            const int lo = bands.lower[b], n = bands.nLines[b];
-            double mx = 0.0, sm = 0.0;
-            for (int i = lane; i < n; i += 32) {
-                double a = fabs(S.lines[lo + i]);
-                mx = fmax(mx, a);
-                sm += a;
-            }
-#pragma unroll
-            for (int o = 16; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-            sm = warp_sum(sm);
-            if (mx > 0.0) {
-                double mean = sm / (double)n;
-                for (int i = lane; i < n; i += 32) S.lines[lo + i] *= smooth[lo - cut + i] / mean;
-            }
-        }
-        __syncthreads();
-    }
-    // (4) undo the overall scale, IMDCT, synthesis window (coder/codec.py:85-89)
-    const double inv = 1.0 / (double)(1 << scale);
-    const cplx<double>* tw = reinterpret_cast<const cplx<double>*>(isLong ? dev->d.tw_mdct_long : dev->d.tw_mdct_short);
-    const cplx<double>* roots = reinterpret_cast<const cplx<double>*>(dev->d.tw_fft[isLong ? 2 : 0]);
-    cplx<double>* fbuf = reinterpret_cast<cplx<double>*>(S.wsA);
-    double* v = S.wsA + 1024;
-    imdct_pre<double, N, 1, DEC_NT>(S.lines, inv, tw, fbuf, tid);
-    __syncthreads();
-    cta_fft<double, Q, 1, DEC_NT>(fbuf, roots, tid);
-    mdct_post<double, N, 1, DEC_NT>(fbuf, tw, 1.0, v, tid);
-    __syncthreads();
-    const double* w = (isLong ? dev->d.win_long : dev->d.win_short) + shape * N;
-    for (int i = tid; i < N; i += DEC_NT) S.y[yOff + i] += w[i] * imdct_sample<double, N>(v, i);
-    __syncthreads();
 }
 
 struct DecArgs {

@@ -1,0 +1,253 @@
+// Per-frame encoder (device functions shared by the fused stream kernel in encode.cu
+// and the per-function ops in ops.cu): window + MDCT, overall scale, psychoacoustic
+// SMRs, bit allocation, PVQ / block-FP quantisation and MSB-first packing of one frame
+// (coder/codec.py:266-380, :426-555; coder/pacfile.py:363-447).  CTA-cooperative:
+// every thread of an ENC_NT-thread CTA calls encode_frame.
+#pragma once
+#include "bitalloc.cuh"
+#include "mdct.cuh"
+#include "psy.cuh"
+#include "pvq.cuh"
+
+#define ENC_NT 256
+#define REC_STRIDE 2176          // bytes per channel-block scratch record (>= worst-case declared size)
+#define REC_WORDS (REC_STRIDE / 4)
+#define BAND_WORDS 640
+
+// int16 PCM -> signed fraction (coder/pcmfile.py:89-98): 2|c|/65535 with the sign
+// restored; -32768 has magnitude bits 0 and maps to 0.0.
+__device__ __forceinline__ double pcm_to_double(short c) {
+    int m = c < 0 ? -(int)c : (int)c;
+    m &= 0x7fff;
+    double v = (double)(2 * m) / 65535.0;
+    return c < 0 ? -v : v;
+}
+
+// ---------------------------------------------------------------- per-frame encode
+struct EncSmem {
+    double* xs;        // [2048] frame samples; later PVQ workspace A
+    double* fb;        // [2048] FFT buffer / masker list; later PVQ workspace B
+    double* lines;     // [1024] MDCT lines (scaled)
+    double* mk;        // [1040] |X| -> intensity -> masked threshold; later PVQ pulse ints
+    double* smr;       // [32]
+    double* tmp;       // [32]
+    unsigned* blockbuf;  // [REC_WORDS] the channel-block bitstream (big-endian words)
+    unsigned* bandbits;  // [BAND_WORDS] per-band private bit buffers
+    int* ba;           // [32] bit allocation
+    int* nlEff;        // [32] lines per band as the allocator sees them (1 for SBR-omitted)
+    int* used;         // [32] bits emitted per band
+    int* wordOff;      // [33]
+    int* capOff;       // [33] pow2 workspace offsets
+    int* sfb;          // [32] BFP scale factors
+    int* misc;         // [16]
+    double* red;       // [16] reduction scratch
+    double* env;       // [32] SBR: sum of |X|/H over each omitted band
+    // optional per-band field log (global memory, [nBands][logCap]); nullptr in the stream kernel
+    unsigned long long* logVal;
+    int* logW;
+    int* logCnt;       // [nBands]
+    int logCap;
+};
+
+__device__ __forceinline__ double block_max(double v, double* red, int tid) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        double t = __shfl_xor_sync(0xffffffffu, v, o);
+        v = t > v ? t : v;
+    }
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    double r = red[0];
+#pragma unroll
+    for (int w = 1; w < ENC_NT / 32; ++w) r = red[w] > r ? red[w] : r;
+    return r;
+}
+
+// Encode one frame of N samples at fx (shared) and append its fields to the block
+// bitstream at bit position *bpos.  Returns the DECLARED size in bits
+// (getNumBytesNeeded, coder/pacfile.py:342-361).  sbr: long frame of an SBR stream.
+template <int N>
+__device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const double* fx, int shape, bool cur,
+                            bool lastOrNext, bool sbr, int* bpos, int* err) {
+    constexpr int H = N / 2, Q = N / 4;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
+    const int nB = bands.nBands;
+    const PsyConst pc = psy_const<N>(dev);
+    const double* winTab = (N == PAC_NLONG) ? dev->d.win_long : dev->d.win_short;
+    const cplx<double>* tw = reinterpret_cast<const cplx<double>*>(N == PAC_NLONG ? dev->d.tw_mdct_long : dev->d.tw_mdct_short);
+    const cplx<double>* rootsQ = reinterpret_cast<const cplx<double>*>(dev->d.tw_fft[N == PAC_NLONG ? 2 : 0]);
+    cplx<double>* fbuf = reinterpret_cast<cplx<double>*>(S.fb);
+
+    // (1) window + MDCT (coder/codec.py:301-305)
+    mdct_fold<double, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
+    __syncthreads();
+    cta_fft<double, Q, 1, ENC_NT>(fbuf, rootsQ, tid);
+    mdct_post<double, N, 1, ENC_NT>(fbuf, tw, 2.0 / (double)N, S.lines, tid);
+    __syncthreads();
+    double mx = 0.0;
+    for (int i = tid; i < H; i += ENC_NT) mx = fmax(mx, fabs(S.lines[i]));
+    double maxLine = block_max(mx, S.red, tid);
+
+    // (2) Hann FFT magnitude (shared by the psychoacoustic model and the SBR envelope)
+    hann_rfft_mag<N, ENC_NT>(fx, pc, fbuf, S.mk, tid);
+    if (sbr) {                                    // coder/codec.py:460-473
+        double m2 = 0.0;
+        for (int k = tid; k <= H; k += ENC_NT) m2 = fmax(m2, S.mk[k]);
+        double maxFFT = block_max(m2, S.red, tid) / (double)H;
+        maxLine = fmax(maxLine, maxFFT);
+        // per omitted band: sum of fftLines = |X|/H over the band (scale applied later, exact)
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            if (!bands.omitted[b]) continue;
+            double a = 0.0;
+            for (int i = lane; i < bands.nLines[b]; i += 32) a += S.mk[bands.lower[b] + i] / (double)H;
+            a = warp_sum(a);
+            if (lane == 0) S.env[b] = a;
+        }
+        __syncthreads();
+    }
+    const int scale = scale_factor(maxLine, dev->nScaleBits, 5);      // codec.py:308-311 (default nMantBits)
+    const double up = (double)(1 << scale);
+    for (int i = tid; i < H; i += ENC_NT) S.lines[i] *= up;
+    for (int k = tid; k <= H; k += ENC_NT) {
+        double m = S.mk[k];
+        S.mk[k] = pc.norm * (m * m);
+    }
+    __syncthreads();
+
+    // (3) psychoacoustic model -> SMR per band
+    double* mz = S.fb;
+    double* ms = S.fb + 640;
+    double* mkk = S.fb + 1280;
+    pick_maskers<N, ENC_NT>(S.mk, pc, mz, ms, mkk, &S.misc[0], tid);
+    const int nMask = S.misc[0];
+    masked_threshold<N, ENC_NT>(pc, mz, ms, mkk, nMask, S.mk, tid);
+    band_smr<ENC_NT>(S.lines, scale, S.mk, bands, S.smr, tid);
+
+    // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)
+    if (tid < nB) S.nlEff[tid] = (sbr && bands.omitted[tid]) ? 1 : bands.nLines[tid];
+    __syncthreads();
+    if (warp == 0) {
+        int nfb = H;
+        if (!sbr) {
+            if (cur) nfb = (int)(1.45 * H);
+            if (lastOrNext) nfb = (int)(0.85 * nfb);
+        }
+        double budget = dev->targetBitsPerSample * (double)nfb;
+        if (dev->useVQ) budget -= (double)dev->nScaleBits;
+        else budget -= (double)(dev->nScaleBits * (nB + 1));
+        budget -= (double)(dev->nMantSizeBits * nB);
+        warp_bit_alloc(budget, dev->maxMantBits, nB, S.nlEff, S.smr, S.tmp, S.ba);
+    }
+    __syncthreads();
+
+    // (5) quantise each coded band into its private bit buffer
+    if (tid == 0) {
+        int w = 0, c = 0;
+        for (int b = 0; b < nB; ++b) {
+            S.wordOff[b] = w;
+            S.capOff[b] = c;
+            int bits = S.ba[b] * S.nlEff[b];
+            w += (bits + 31) / 32 + 3;                    // slack: a 64-bit put may straddle
+            int cap = 1;
+            while (cap < bands.nLines[b]) cap <<= 1;
+            c += cap;
+        }
+        S.wordOff[nB] = w;
+        S.capOff[nB] = c;
+        if (w > BAND_WORDS || c > (N == PAC_NLONG ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
+    }
+    for (int i = tid; i < BAND_WORDS; i += ENC_NT) S.bandbits[i] = 0u;
+    __syncthreads();
+    if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (N == PAC_NLONG ? 2048 : 256)) return 0;
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab};
+    int* yws = reinterpret_cast<int*>(S.mk);              // masked threshold is dead from here on
+    // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
+    // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
+    double* wsA = (N == PAC_NLONG) ? S.xs : S.lines + 256;
+    double* wsB = (N == PAC_NLONG) ? S.fb : S.lines + 512;
+    if (dev->useVQ) {
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            int used = 0;
+            if (S.ba[b]) {
+                const int cap = S.capOff[b + 1] - S.capOff[b];
+                BitW bw = {S.bandbits + S.wordOff[b], 0};
+                int werr = 0;
+                FieldLog flog = {S.logVal + (size_t)b * S.logCap, S.logW + (size_t)b * S.logCap, S.logCnt + b, S.logCap};
+                FieldLog* lg = S.logVal ? &flog : nullptr;
+                if (sbr && bands.omitted[b]) {
+                    // one value: mean |fftLines| of the band (coder/codec.py:508-510)
+                    __shared__ double s_env[ENC_NT / 32];
+                    if (lane == 0) s_env[warp] = (S.env[b] * up) / (double)bands.nLines[b];
+                    __syncwarp();
+                    used = warp_quantize_gain_shape(pt, &s_env[warp], 1, S.ba[b], wsA + S.capOff[b],
+                                                    wsB + S.capOff[b], yws + S.capOff[b], cap, bw, &werr, lg);
+                } else {
+                    used = warp_quantize_gain_shape(pt, S.lines + bands.lower[b], bands.nLines[b],
+                                                    S.ba[b] * bands.nLines[b], wsA + S.capOff[b],
+                                                    wsB + S.capOff[b], yws + S.capOff[b], cap, bw, &werr, lg);
+                }
+                if (werr && lane == 0) atomicOr(err, werr);
+            }
+            if (lane == 0) {
+                S.used[b] = used;
+                if (used == 0) S.ba[b] = 0;               // coder/codec.py:352-353
+            }
+        }
+    } else {
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            const int lo = bands.lower[b], n = bands.nLines[b], bb = S.ba[b];
+            double m = 0.0;
+            for (int i = lane; i < n; i += 32) m = fmax(m, fabs(S.lines[lo + i]));
+#pragma unroll
+            for (int o = 16; o; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+            const int sf = scale_factor(m, dev->nScaleBits, bb);       // coder/codec.py:369-371
+            if (bb)
+                for (int i = lane; i < n; i += 32)
+                    bw_put_at(S.bandbits + S.wordOff[b], i * bb,
+                              mantissa_bfp(S.lines[lo + i], sf, dev->nScaleBits, bb), bb);
+            if (lane == 0) {
+                S.sfb[b] = sf;
+                S.used[b] = bb * n;
+            }
+        }
+    }
+    __syncthreads();
+
+    // (6) frame header + band payload positions (coder/pacfile.py:363-447), thread 0
+    if (tid == 0) {
+        BitW bw = {S.blockbuf, *bpos};
+        bw_put(bw, (unsigned long long)scale, dev->nScaleBits);
+        int declared = dev->nScaleBits;
+        if (dev->useVQ)
+            for (int b = 0; b < nB; ++b) bw_put(bw, S.ba[b] ? S.ba[b] - 1 : 0, dev->nMantSizeBits);
+        for (int b = 0; b < nB; ++b) {
+            if (!dev->useVQ) {
+                bw_put(bw, S.ba[b] ? S.ba[b] - 1 : 0, dev->nMantSizeBits);
+                bw_put(bw, (unsigned long long)S.sfb[b], dev->nScaleBits);
+            }
+            int u = S.ba[b] ? S.used[b] : 0;
+            S.capOff[b] = bw.pos;                         // reuse: destination bit position of band b
+            bw.pos += u;
+            declared += dev->nMantSizeBits + dev->nScaleBits;
+            if (S.ba[b]) declared += (sbr && bands.omitted[b]) ? S.ba[b] : S.ba[b] * bands.nLines[b];
+        }
+        *bpos = bw.pos;
+        S.misc[2] = declared;
+        S.misc[5] = scale;
+    }
+    __syncthreads();
+    // (7) merge the band buffers into the block bitstream (disjoint bit ranges)
+    for (int b = warp; b < nB; b += ENC_NT / 32) {
+        const int u = S.ba[b] ? S.used[b] : 0;
+        const unsigned* src = S.bandbits + S.wordOff[b];
+        for (int i = lane; i * 32 < u; i += 32) {
+            int nb = min(32, u - i * 32);
+            bw_put_at(S.blockbuf, S.capOff[b] + i * 32, (unsigned long long)(src[i] >> (32 - nb)), nb);
+        }
+    }
+    __syncthreads();
+    return S.misc[2];
+}
+

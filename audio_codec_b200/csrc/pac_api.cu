@@ -3,6 +3,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <vector>
 #include "pac_api.h"
 
@@ -88,6 +89,45 @@ static void make_bands(int nLines, int fs, PacBands* b) {
         b->lower[k] = lo;
         lo += nl[k];
     }
+}
+
+// Window of any length for the window.* drop-ins (coder/window.py:14-92), cached per context.
+int pac_window_table(pac_ctx* c, int kind, int N, int Ns, double alpha, const double** d, const float** f) {
+    if (N < 1 || kind < 0 || kind > PAC_W_HANN || kind == PAC_W_NONE) return PAC_ERR_ARG;
+    const bool edler = kind == PAC_W_START || kind == PAC_W_STOP || kind == PAC_W_STARTSTOP;
+    if (edler && (Ns < 2 || Ns > N || (N % 4) || (Ns % 4))) return PAC_ERR_ARG;
+    if (!edler) Ns = 0;
+    if (kind != PAC_W_KAISER) alpha = 0.0;
+    for (auto& e : c->winCache)
+        if (e.kind == kind && e.N == N && e.Ns == Ns && e.alpha == alpha) { *d = e.d; *f = e.f; return 0; }
+    std::vector<double> w(N, 0.0);
+    const int pad = N / 4 - Ns / 4;
+    switch (kind) {
+        case PAC_W_SINE: for (int n = 0; n < N; ++n) w[n] = w_sine(n, N); break;
+        case PAC_W_HANN: for (int n = 0; n < N; ++n) w[n] = w_hann(n, N); break;
+        case PAC_W_KAISER: for (int n = 0; n < N; ++n) w[n] = w_kaiser(n, N, alpha); break;
+        case PAC_W_START:
+        case PAC_W_STOP:
+            for (int n = 0; n < N / 2; ++n) w[n] = w_sine(n, N);
+            for (int n = 0; n < pad; ++n) w[N / 2 + n] = 1.0;
+            for (int n = 0; n < Ns / 2; ++n) w[N / 2 + pad + n] = w_sine(Ns / 2 + n, Ns);
+            if (kind == PAC_W_STOP) for (int n = 0; n < N / 2; ++n) std::swap(w[n], w[N - 1 - n]);
+            break;
+        case PAC_W_STARTSTOP:
+            for (int n = 0; n < Ns / 2; ++n) w[pad + n] = w_sine(n, Ns);
+            for (int n = 0; n < 2 * pad; ++n) w[pad + Ns / 2 + n] = 1.0;
+            for (int n = 0; n < Ns / 2; ++n) w[3 * pad + Ns / 2 + n] = w_sine(Ns / 2 + n, Ns);
+            break;
+    }
+    std::vector<float> wf(w.begin(), w.end());
+    pac_ctx::WinEntry e = {kind, N, Ns, alpha, nullptr, nullptr};
+    int rc;
+    if ((rc = upload(c, w, &e.d))) return rc;
+    if ((rc = upload(c, wf, &e.f))) return rc;
+    c->winCache.push_back(e);
+    *d = e.d;
+    *f = e.f;
+    return 0;
 }
 
 template <typename T> static void to_type(const std::vector<long double>& s, std::vector<T>& d) {

@@ -19,8 +19,13 @@ struct pac_ctx {
     size_t ioBytes[2];
     cudaEvent_t ev[4];   // around k_encode and k_decode, for pac_last_kernel_ms
     int evValid[2];
+    // windows of arbitrary length for pac_window, built on demand
+    struct WinEntry { int kind, N, Ns; double alpha; const double* d; const float* f; };
+    std::vector<WinEntry> winCache;
 };
 
 int pac_scratch(pac_ctx* ctx, size_t bytes, void** out);
 int pac_pinned(pac_ctx* ctx, size_t bytes, void** out);
 int pac_io(pac_ctx* ctx, int which, size_t bytes, void** out);
+// window table of length N (kind: PAC_W_*, Ns = short length for the Edler shapes)
+int pac_window_table(pac_ctx* ctx, int kind, int N, int Ns, double alpha, const double** d, const float** f);

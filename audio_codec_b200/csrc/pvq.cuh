@@ -170,6 +170,22 @@ __device__ __forceinline__ unsigned long long warp_quantize_pvq(const PvqTab& t,
 
 struct PvqNode { short off, cap, n, buf; int bits; };
 
+// Optional record of the (index, width) fields a band emits, in stream order: what
+// quantize_gain_shape returns as two Python lists (coder/gain_shape_quantize.py:476-512).
+// Written by lane 0 only; nullptr in the fused stream kernels.
+struct FieldLog {
+    unsigned long long* val;
+    int* width;
+    int* count;     // fields recorded so far
+    int cap;
+};
+__device__ __forceinline__ void log_field(FieldLog* lg, unsigned long long v, int w) {
+    if (!lg) return;
+    int i = *lg->count;
+    if (i < lg->cap) { lg->val[i] = v; lg->width[i] = w; }
+    *lg->count = i + 1;
+}
+
 // quantize_gain_shape for one band on one warp.
 //   x[0..L)   band lines (shared, read only)
 //   wsA/wsB   double workspaces, this band's region of capacity cap = pow2 >= L
@@ -177,7 +193,8 @@ struct PvqNode { short off, cap, n, buf; int bits; };
 //   out       bit writer positioned at this band's private bit buffer
 // Returns the number of bits written (0: all-zero band, caller zeroes bitAlloc).
 __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const double* x, int L, int R, double* wsA,
-                                                        double* wsB, int* yws, int cap, BitW& out, int* err) {
+                                                        double* wsB, int* yws, int cap, BitW& out, int* err,
+                                                        FieldLog* lg = nullptr) {
     const int lane = threadIdx.x & 31;
     int bg, bs;
     gs_alloc(t, R, L, &bg, &bs);
@@ -200,7 +217,7 @@ __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const d
             if (nd.bits <= PVQ_SPLIT_BITS) {
                 int w;
                 unsigned long long idx = warp_quantize_pvq(t, cur, oth, yws + nd.off, nd.n, nd.bits, &w, err);
-                if (lane == 0) bw_put(out, idx, w);
+                if (lane == 0) { bw_put(out, idx, w); log_field(lg, idx, w); }
                 used += w;
                 continue;
             }
@@ -230,7 +247,7 @@ __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const d
             unsigned long long ti = quantize_uniform(theta / hp, aT);
             double tq = dequantize_uniform(ti, aT) * hp;
             ms_alloc(aMs, tq, half, &aMid, &aSide);
-            if (lane == 0) bw_put(out, ti, aT);
+            if (lane == 0) { bw_put(out, ti, aT); log_field(lg, ti, aT); }
             used += aT;
             if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
             if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide};
@@ -243,7 +260,7 @@ __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const d
     if (bg < 0) bg = 0;
     if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
     unsigned long long gi = quantize_uniform(g, bg);
-    if (lane == 0) bw_put(out, gi, bg);
+    if (lane == 0) { bw_put(out, gi, bg); log_field(lg, gi, bg); }
     __syncwarp();
     return total + bg;
 }

@@ -51,9 +51,9 @@ __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b
 
 struct DecNode { short off, cap, n, buf; int bits; double theta; short state, root; };
 
-// dequantize_gain_shape for one band on one warp.  Reads exactly R bits from br
-// (all lanes hold the same cursor).  out[0..L) <- gain * shape.
-__device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR br, int R, int L, double* wsA,
+// dequantize_gain_shape for one band on one warp.  Reads its fields from br and
+// leaves the cursor after them (all lanes hold the same cursor).  out[0..L) <- gain * shape.
+__device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR& br, int R, int L, double* wsA,
                                                            double* wsB, int cap, double* out, int* err) {
     const int lane = threadIdx.x & 31;
     int bg, bs;

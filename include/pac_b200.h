@@ -31,7 +31,8 @@ enum pac_status {
 };
 /* window shapes: coder/window.py:14 SineWindow, :61 StartWindow, :73 StopWindow,
  * :82 StartStopWindow, :45 KBDWindow (a Kaiser window, alpha = 4), none */
-enum pac_window { PAC_W_SINE = 0, PAC_W_START = 1, PAC_W_STOP = 2, PAC_W_STARTSTOP = 3, PAC_W_KAISER = 4, PAC_W_NONE = 5 };
+enum pac_window { PAC_W_SINE = 0, PAC_W_START = 1, PAC_W_STOP = 2, PAC_W_STARTSTOP = 3, PAC_W_KAISER = 4, PAC_W_NONE = 5,
+                  PAC_W_HANN = 6 /* coder/window.py:29 HanningWindow; pac_window only */ };
 
 /* The fields of the reference's CodingParams bag the path reads
  * (coder/pacfile.py:157-174, :699-707). */
@@ -119,6 +120,100 @@ int pac_decode_host(pac_ctx* ctx, const unsigned char* h_pac, const long long* h
  * kernel (k_encode / k_decode) of the last encode / decode call on this context,
  * from CUDA events recorded on the caller's stream; -1 if none yet. */
 int pac_last_kernel_ms(pac_ctx* ctx, float* enc_ms, float* dec_ms);
+
+
+/* ======================================================================================
+ * Per-function ops: the reference's Python function surface, one batched call each.
+ * All pointers are DEVICE pointers unless named h_*; rows are contiguous.
+ * ====================================================================================== */
+
+/* window.SineWindow / HanningWindow / KBDWindow(alpha) / StartWindow / StopWindow /
+ * StartStopWindow (coder/window.py:14-92): d_out[r][n] = w[n] * d_x[r][n], any N; n_short is
+ * N_short of the Edler shapes (N_long = N); alpha only for PAC_W_KAISER. */
+int pac_window(pac_ctx* ctx, int dtype, const void* d_x, long long n_rows, int N, int window, int n_short,
+               double alpha, void* d_out, void* stream);
+
+/* detect_transients.parTransientDetect(block, thresh, axis=1) (coder/detect_transients.py:5-23)
+ * on n_blocks blocks of [n_channels][len] doubles; d_flags[b] = 1 if transient. */
+int pac_transient_detect(pac_ctx* ctx, const double* d_blocks, long long n_blocks, int n_channels, int len,
+                         double thresh, unsigned char* d_flags, void* stream);
+
+/* psychoac.CalcSMRs / getMaskedThreshold (coder/psychoac.py:163-291) for n_frames frames of
+ * N (2048 | 256) samples at the context's sample rate.  d_mdct: MDCT lines scaled by 2^d_scale[f].
+ * Bands as ScaleFactorBands gives them (lowerLine, nLines).  d_smr [n][n_bands] and/or
+ * d_mask [n][N/2] (masked threshold in dB SPL at the MDCT lines); either may be NULL. */
+int pac_calc_smr(pac_ctx* ctx, const double* d_data, const double* d_mdct, const int* d_scale, long long n_frames,
+                 int N, int n_bands, const int* h_lower, const int* h_nlines, double* d_smr, double* d_mask,
+                 void* stream);
+
+/* psychoac.SPL (array form) / Intensity / Bark / Thresh (coder/psychoac.py:10-48), elementwise;
+ * op: 0 SPL, 1 Intensity, 2 Bark, 3 Thresh. */
+int pac_psy_map(pac_ctx* ctx, int op, const double* d_x, long long n, double* d_out, void* stream);
+
+/* bitalloc.BitAlloc(bitBudget, maxMantBits, nBands, nLines, SMR) (coder/bitalloc.py:62-121);
+ * BitAlloc_SBR is the same call with nLines[omitted] = 1 (coder/bitalloc.py:123-145). */
+int pac_bit_alloc(pac_ctx* ctx, const double* d_budget, int max_mant_bits, int n_bands, const int* h_nlines,
+                  const double* d_smr, long long n_frames, int* d_bits, void* stream);
+
+/* quantize.vQuantizeUniform / vDequantizeUniform / ScaleFactor / vMantissa / vDequantize
+ * (coder/quantize.py:61-125, :229-274), elementwise over n values. */
+int pac_quantize_uniform(pac_ctx* ctx, const double* d_x, long long n, int n_bits, long long* d_code, void* stream);
+int pac_dequantize_uniform(pac_ctx* ctx, const long long* d_code, long long n, int n_bits, double* d_x, void* stream);
+int pac_scale_factor(pac_ctx* ctx, const double* d_x, long long n, int n_scale_bits, int n_mant_bits,
+                     long long* d_scale, void* stream);
+int pac_mantissa(pac_ctx* ctx, const double* d_x, long long n, int scale, int n_scale_bits, int n_mant_bits,
+                 long long* d_mant, void* stream);
+int pac_dequantize(pac_ctx* ctx, int scale, const long long* d_mant, long long n, int n_scale_bits, int n_mant_bits,
+                   double* d_x, void* stream);
+
+/* gain_shape_quantize.quantize_gain_shape(x, bit_alloc, k_fine=0) (coder/gain_shape_quantize.py:476-512)
+ * for n_vec vectors of length L with budgets d_bit_alloc[v] (<= max_bit_alloc): the (index, width)
+ * fields in stream order go to d_idx/d_bits [v][max_fields], their number to d_nfields[v].
+ * Synchronises; *h_err receives soft-error flags (inputs undefined in the reference). */
+int pac_gain_shape_quantize(pac_ctx* ctx, const double* d_x, int L, long long n_vec, const int* d_bit_alloc,
+                            int max_bit_alloc, unsigned long long* d_idx, int* d_bits, int* d_nfields,
+                            int max_fields, int* h_err, void* stream);
+/* gain_shape_quantize.dequantize_gain_shape(pb, bit_alloc, L, k_fine=0) (:515-538): vector v is
+ * parsed from the shared byte buffer starting at bit d_bitpos[v]; the cursor after its fields is
+ * returned in d_bitpos_out[v]. */
+int pac_gain_shape_dequantize(pac_ctx* ctx, const unsigned char* d_bytes, long long n_bytes, const long long* d_bitpos,
+                              const int* d_bit_alloc, int L, long long n_vec, double* d_out, long long* d_bitpos_out,
+                              int* h_err, void* stream);
+
+/* bitpack.PackedBits.WriteBits / ReadBits (coder/bitpack.py:37-175): row r packs its
+ * d_count[r] fields (value, width <= 64) MSB-first into row_bytes bytes (multiple of 4). */
+int pac_pack_bits(pac_ctx* ctx, const unsigned long long* d_val, const int* d_width, const int* d_count,
+                  int max_fields, long long n_rows, int row_bytes, unsigned char* d_out, int* h_err, void* stream);
+int pac_unpack_bits(pac_ctx* ctx, const unsigned char* d_in, int row_bytes, const long long* d_start_bit,
+                    const int* d_width, const int* d_count, int max_fields, long long n_rows,
+                    unsigned long long* d_val, void* stream);
+
+/* PACFile.WriteDataBlock for n channel-blocks (coder/pacfile.py:449-610): d_frames [n][2048] =
+ * priorBlock || data as signed fractions, d_flags[n] = last | cur<<1 | next<<2.  d_rec
+ * [n][pac_record_stride()] receives the packed payload (flag bits, frame(s), zero padding),
+ * d_rec_bytes[n] the declared size (getNumBytesNeeded), d_zero_sub[n] = 1 if a short sub-frame
+ * is all zero (the block is then dropped by the reference, :503-506). */
+int pac_record_stride(void);
+int pac_encode_blocks(pac_ctx* ctx, const double* d_frames, const unsigned char* d_flags, long long n,
+                      unsigned char* d_rec, int* d_rec_bytes, unsigned char* d_zero_sub, int* h_err, void* stream);
+/* codec.EncodeSingleChannel / EncodeSingleChannel_SBR (coder/codec.py:266-380, :426-555) for n
+ * frames of N samples: overall scale, bit allocation [n][32], BFP scale factors [n][32], bits
+ * emitted per band [n][32], the frame's packed fields (d_rec, d_rec_bits = bit count) and, for
+ * VQ, the per-band field log d_log_val/width [n][32][log_cap], d_log_count [n][32]. */
+int pac_encode_frames(pac_ctx* ctx, const double* d_data, int N, const unsigned char* d_flags, int sbr, long long n,
+                      int* d_scale, int* d_bit_alloc, int* d_scale_factor, int* d_band_bits, unsigned char* d_rec,
+                      int* d_rec_bits, unsigned long long* d_log_val, int* d_log_width, int* d_log_count, int log_cap,
+                      int* h_err, void* stream);
+/* PACFile.ReadDataBlock's per-channel work (coder/pacfile.py:256-287): payload records ->
+ * 2048 windowed samples each, before the block overlap-add. */
+int pac_decode_blocks(pac_ctx* ctx, const unsigned char* d_rec, int rec_stride, const int* d_rec_bytes, long long n,
+                      double* d_out, int* h_err, void* stream);
+/* codec.Decode / Decode_SBR (coder/codec.py:47-222): one frame per record, fields from bit 0
+ * (overall scale, bit allocations, [scale factors,] band payloads) -> N windowed samples;
+ * d_bits_consumed[n] = bit cursor after the frame. */
+int pac_decode_frames(pac_ctx* ctx, const unsigned char* d_rec, int rec_stride, const int* d_rec_bytes, int N,
+                      const unsigned char* d_flags, long long n, double* d_out, int* d_bits_consumed, int* h_err,
+                      void* stream);
 
 #ifdef __cplusplus
 }
