@@ -156,11 +156,13 @@ __device__ __forceinline__ unsigned long long warp_quantize_pvq(const PvqTab& t,
         }
         long long k = K - carry - (inc - a);           // pulses left when element i is reached
         if (a > 0) {
+            // N(l-1,k) + 2 sum_{j<a} N(l-1,k-j) counts the vectors whose first component is smaller in
+            // magnitude than a: N(l,k) - N(l,k-a) - N(l-1,k-a) (pvq_first_below)
             int l = n - i;
             bool neg = vec[i] < 0.0;
-            unsigned long long c = pvq_N(t, l - 1, k);
-            for (int j = 1; j < a; ++j) c += 2ull * pvq_N(t, l - 1, k - j);
-            if (neg) c += pvq_N(t, l - 1, k - a);
+            unsigned long long below = pvq_N(t, l - 1, k - a);
+            unsigned long long c = pvq_N(t, l, k) - pvq_N(t, l, k - a) - below;
+            if (neg) c += below;
             acc += c;
         }
         carry += __shfl_sync(FULL, inc, 31);

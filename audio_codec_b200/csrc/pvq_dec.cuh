@@ -6,46 +6,42 @@
 #pragma once
 #include "pvq.cuh"
 
-// Fischer index -> pulse vector (the reference's recursive step_1..step_5 walk).
-// Serial; run by one lane.  x[0..L) receives signed pulse counts as doubles.
+// Fischer index -> pulse vector: the inverse of encode_pvq_vector, i.e. what the reference's
+// recursive step_1..step_5 walk produces for a valid index (coder/gain_shape_quantize.py:127-186).
+// Element i with l components and k pulses left: codes [0, N(l-1,k)) have x_i = 0; then for
+// j = 1..k a block of N(l-1,k-j) codes with x_i = +j and one with x_i = -j.  The +j block starts
+// at A(j) = N(l,k) - N(l,k-j) - N(l-1,k-j) (the number of vectors with |x_i| < j), so j is found by
+// bisection instead of the reference's linear scan.  Serial; run by ONE thread.  x[0..L) receives
+// the signed pulse counts as doubles.
 __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b, int L, long long K, double* x,
                                            int* err) {
-    for (int i = 0; i < L; ++i) x[i] = 0.0;
-    unsigned long long xb = 0ull;
     long long k = K;
-    int l = L, i = 0;
-    int guard = 0;
-    while (true) {
-        if (++guard > 100000 || i >= L) { *err |= PVQ_ERR_DEGENERATE; return; }
-        if (b == xb) {                                    // step 1 (+ step 5)
-            x[i] = 0.0;
-            if (k > 0) x[L - 1] = (double)k;
-            return;
+    unsigned long long r = b;
+    int i = 0;
+    for (; i < L && k > 0; ++i) {
+        const int l = L - i;
+        if (r == 0ull) break;                             // step 1 + 5: the rest of the pulses sit on the last component
+        const unsigned long long n0 = pvq_N(t, l - 1, k);
+        if (r < n0) { x[i] = 0.0; continue; }
+        const unsigned long long nlk = pvq_N(t, l, k);
+        long long lo = 1, hi = k;
+        while (lo < hi) {
+            long long mid = (lo + hi + 1) >> 1;
+            unsigned long long a = nlk - pvq_N(t, l, k - mid) - pvq_N(t, l - 1, k - mid);
+            if (a <= r) lo = mid; else hi = mid - 1;
         }
-        unsigned long long n0 = pvq_N(t, l - 1, k);       // step 2
-        long long xi = 0;
-        if (b >= xb + n0) {
-            xb += n0;
-            long long j = 1;
-            bool found = false;
-            while (true) {                                // step 3
-                if (j > k) j = k;
-                unsigned long long nj = pvq_N(t, l - 1, k - j);
-                if (b < xb + 2ull * nj) {
-                    xi = (b >= xb + nj) ? -j : j;
-                    found = true;
-                    break;
-                }
-                xb += 2ull * nj;
-                if (j < k) ++j; else break;
-            }
-            if (!found) continue;                         // reference jumps back to step 1
-        }
-        x[i] = (double)xi;                                // step 4
-        k -= xi < 0 ? -xi : xi;
-        l -= 1;
-        i += 1;
-        if (k <= 0) return;
+        const unsigned long long nj = pvq_N(t, l - 1, k - lo);
+        r -= nlk - pvq_N(t, l, k - lo) - nj;
+        bool neg = false;
+        if (r >= nj) { neg = true; r -= nj; }
+        if (r >= nj) { *err |= PVQ_ERR_DEGENERATE; r = 0ull; }    // index outside the codebook
+        x[i] = neg ? -(double)lo : (double)lo;
+        k -= lo;
+    }
+    for (; i < L; ++i) x[i] = 0.0;
+    if (k > 0) {
+        if (r != 0ull) *err |= PVQ_ERR_DEGENERATE;
+        x[L - 1] = (double)k;
     }
 }
 

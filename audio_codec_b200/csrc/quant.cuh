@@ -108,13 +108,24 @@ struct BitR {
     long long pos;            // bit cursor
     long long end;            // total bits available
 };
+// Next n (<= 64) bits, MSB first; bits past `end` (a whole number of bytes) read as 0.
 __device__ __forceinline__ unsigned long long br_get(BitR& r, int n) {
-    unsigned long long v = 0;
-    for (int i = 0; i < n; ++i) {
-        unsigned bit = 0;
-        if (r.pos < r.end) bit = (r.p[r.pos >> 3] >> (7 - (r.pos & 7))) & 1u;
-        v = (v << 1) | bit;
-        ++r.pos;
+    if (n <= 0) return 0ull;
+    const long long pos = r.pos;
+    r.pos = pos + n;
+    const long long byte = pos >> 3, endByte = r.end >> 3;
+    const int off = (int)(pos & 7);
+    const int nb = (off + n + 7) >> 3;               // bytes touched, <= 9
+    unsigned long long hi = 0ull;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        unsigned b = (i < nb && byte + i < endByte) ? r.p[byte + i] : 0u;
+        hi = (hi << 8) | b;
     }
-    return v;
+    unsigned long long v = hi << off;
+    if (nb == 9) {
+        unsigned b8 = (byte + 8 < endByte) ? r.p[byte + 8] : 0u;
+        v |= (unsigned long long)(b8 >> (8 - off));
+    }
+    return n == 64 ? v : v >> (64 - n);
 }
