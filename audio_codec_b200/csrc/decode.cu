@@ -49,18 +49,7 @@ __global__ void __launch_bounds__(DEC_NT)
 k_decode(const PacDev* __restrict__ dev, DecArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DecSmem S;
-    double* dp = reinterpret_cast<double*>(smem_raw);
-    S.lines = dp; dp += 1024;
-    S.wsA = dp; dp += 2048;
-    S.wsB = dp; dp += 2048;
-    S.y = dp; dp += 2048;
-    int* ip = reinterpret_cast<int*>(dp);
-    S.ba = ip; ip += 32;
-    S.sfb = ip; ip += 32;
-    S.bandPos = ip; ip += 34;
-    S.capOff = ip; ip += 34;
-    S.misc = ip; ip += 16;
-    S.rec = reinterpret_cast<unsigned char*>(ip);
+    dec_smem_carve(smem_raw, S);
     const int tid = threadIdx.x;
     const int cb = blockIdx.x;
     int nBytes = a.payBytes[cb];
@@ -206,7 +195,7 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
         DecArgs a;
         a.buf = d_pac; a.payOff = (long long*)(sb + oPay); a.payBytes = (int*)(sb + oPayB);
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
-        size_t smem = (1024 + 2048 * 3) * sizeof(double) + (32 * 2 + 34 * 2 + 16) * sizeof(int) + DEC_REC_MAX;
+        size_t smem = dec_smem_bytes();
         PAC_CHECK(cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaEventRecord(ctx->ev[2], st);
         k_decode<<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);

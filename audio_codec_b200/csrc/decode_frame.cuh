@@ -8,6 +8,7 @@
 
 #define DEC_NT 256
 #define DEC_REC_MAX 4096          // largest channel-block payload accepted (bytes)
+#define DEC_MAX_NODES 896         // split-tree nodes per frame (a 128 kb/s long frame has ~150)
 
 struct DecSmem {
     unsigned char* rec;   // [DEC_REC_MAX] payload bytes
@@ -19,8 +20,32 @@ struct DecSmem {
     int* sfb;             // [32]
     int* bandPos;         // [33] bit position of each band's payload
     int* capOff;          // [33]
-    int* misc;            // [16]
+    int* misc;            // [16]; [7] = number of tree nodes of the current frame
+    DNode* nodes;         // [DEC_MAX_NODES] split-tree nodes of the current frame (phase A -> B -> C)
+    BandDec* bd;          // [32]
 };
+
+__host__ __device__ constexpr size_t dec_smem_bytes() {
+    return (1024 + 2048 * 3) * sizeof(double) + DEC_MAX_NODES * sizeof(DNode) + 32 * sizeof(BandDec) +
+           (32 * 2 + 34 * 2 + 16) * sizeof(int) + DEC_REC_MAX;
+}
+
+__device__ __forceinline__ void dec_smem_carve(unsigned char* raw, DecSmem& S) {
+    double* dp = reinterpret_cast<double*>(raw);
+    S.lines = dp; dp += 1024;
+    S.wsA = dp; dp += 2048;
+    S.wsB = dp; dp += 2048;
+    S.y = dp; dp += 2048;
+    S.nodes = reinterpret_cast<DNode*>(dp);
+    S.bd = reinterpret_cast<BandDec*>(S.nodes + DEC_MAX_NODES);
+    int* ip = reinterpret_cast<int*>(S.bd + 32);
+    S.ba = ip; ip += 32;
+    S.sfb = ip; ip += 32;
+    S.bandPos = ip; ip += 34;
+    S.capOff = ip; ip += 34;
+    S.misc = ip; ip += 16;
+    S.rec = reinterpret_cast<unsigned char*>(ip);
+}
 
 // Decode one frame of H = N/2 lines whose fields start at bit *bpos of the record;
 // adds its windowed IMDCT into y[yOff .. yOff+N).
@@ -35,6 +60,7 @@ __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, l
     // (1) frame header: overall scale, bit allocations (+ BFP scale factors): thread 0
     if (tid == 0) {
         BitR br = {S.rec, S.misc[3], recBits};
+        S.misc[7] = 0;
         S.misc[5] = (int)br_get(br, dev->nScaleBits);
         bool anyOm = false;
         if (dev->useVQ) {
@@ -76,29 +102,40 @@ __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, l
     __syncthreads();
     const bool sbr = S.misc[6] != 0;
     const int scale = S.misc[5];
-    // (2) bands in parallel, one warp each
+    // (2) bands: VQ in three phases (parse per band / index decode per leaf / recombine per band),
+    //     block floating point directly
     PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab};
-    int omPos = dev->sbrCutoff;
-    for (int b = warp; b < nB; b += DEC_NT / 32) {
-        const int bb = S.ba[b];
-        if (!bb) continue;
-        const int lo = bands.lower[b], n = bands.nLines[b];
-        if (dev->useVQ) {
+    const int omPos = dev->sbrCutoff;
+    if (dev->useVQ) {
+        for (int b = warp; b < nB; b += DEC_NT / 32) {
+            const int bb = S.ba[b];
+            if (!bb) continue;
             BitR br = {S.rec, S.bandPos[b], recBits};
             int werr = 0;
             const int cap = S.capOff[b + 1] - S.capOff[b];
-            if (sbr && bands.omitted[b]) {
-                // one envelope value, stored at consecutive lines from the cut-off (coder/codec.py:111-132)
+            const bool env = sbr && bands.omitted[b];       // one envelope value (coder/codec.py:111-132)
+            warp_parse_gain_shape(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], S.wsA, S.wsB,
+                                  S.capOff[b], cap, S.nodes, &S.misc[7], DEC_MAX_NODES, &S.bd[b], &werr);
+            if (werr && lane == 0) atomicOr(err, werr);
+        }
+        __syncthreads();
+        cta_decode_leaves(pt, S.nodes, min(S.misc[7], DEC_MAX_NODES), S.wsA, S.wsB, tid, DEC_NT, err);
+        __syncthreads();
+        for (int b = warp; b < nB; b += DEC_NT / 32) {
+            if (!S.ba[b]) continue;
+            double* out = S.lines + bands.lower[b];
+            if (sbr && bands.omitted[b]) {                  // stored at consecutive lines from the cut-off
                 int k = 0;
                 for (int q = 0; q < b; ++q) k += bands.omitted[q] ? 1 : 0;
-                warp_dequantize_gain_shape(pt, br, bb, 1, S.wsA + S.capOff[b], S.wsB + S.capOff[b], cap,
-                                           S.lines + omPos + k, &werr);
-            } else {
-                warp_dequantize_gain_shape(pt, br, bb * n, n, S.wsA + S.capOff[b], S.wsB + S.capOff[b], cap,
-                                           S.lines + lo, &werr);
+                out = S.lines + omPos + k;
             }
-            if (werr && lane == 0) atomicOr(err, werr);
-        } else {
+            warp_finish_gain_shape(S.nodes, S.bd[b], S.wsA, S.wsB, S.capOff[b], out);
+        }
+    } else {
+        for (int b = warp; b < nB; b += DEC_NT / 32) {
+            const int bb = S.ba[b];
+            if (!bb) continue;
+            const int lo = bands.lower[b], n = bands.nLines[b];
             for (int i = lane; i < n; i += 32) {
                 BitR br = {S.rec, (long long)S.bandPos[b] + (long long)i * bb, recBits};
                 unsigned m = (unsigned)br_get(br, bb);

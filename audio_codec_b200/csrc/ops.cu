@@ -725,18 +725,7 @@ __global__ void __launch_bounds__(DEC_NT)
 k_decode_frames(const PacDev* __restrict__ dev, FrameDecArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DecSmem S;
-    double* dp = reinterpret_cast<double*>(smem_raw);
-    S.lines = dp; dp += 1024;
-    S.wsA = dp; dp += 2048;
-    S.wsB = dp; dp += 2048;
-    S.y = dp; dp += 2048;
-    int* ip = reinterpret_cast<int*>(dp);
-    S.ba = ip; ip += 32;
-    S.sfb = ip; ip += 32;
-    S.bandPos = ip; ip += 34;
-    S.capOff = ip; ip += 34;
-    S.misc = ip; ip += 16;
-    S.rec = reinterpret_cast<unsigned char*>(ip);
+    dec_smem_carve(smem_raw, S);
     const int tid = threadIdx.x;
     const long long f = blockIdx.x;
     int nBytes = a.recBytes[f];
@@ -787,7 +776,7 @@ static int run_decode_frames(pac_ctx* ctx, FrameDecArgs& a, long long n, int* h_
     if (rc) return rc;
     PAC_CHECK(cudaMemsetAsync(scr, 0, sizeof(int), st));
     a.err = (int*)scr;
-    size_t smem = (1024 + 2048 * 3) * sizeof(double) + (32 * 2 + 34 * 2 + 16) * sizeof(int) + DEC_REC_MAX;
+    size_t smem = dec_smem_bytes();
     PAC_CHECK(cudaFuncSetAttribute(k_decode_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_decode_frames<<<(unsigned)n, DEC_NT, smem, st>>>(ctx->dev, a);
     OPS_LAUNCH_CHECK();

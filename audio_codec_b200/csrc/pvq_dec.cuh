@@ -137,3 +137,166 @@ __device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR
     for (int i = lane; i < L; i += 32) out[i] = gain * wsA[i];
     __syncwarp();
 }
+
+// ---------------------------------------------------------------------------------------------
+// Three-phase form of dequantize_gain_shape for the fused frame decoder.  The bitstream parse
+// is serial within a band (field widths depend on the theta values just read) but cheap; the
+// expensive part, index -> pulse vector, is independent per leaf.  So:
+//   phase A  warp per band: walk the split tree in stream order, read every field, append one
+//            DNode per tree node to a CTA-wide list (leaves carry their index and K)
+//   phase B  thread per leaf, all threads of the CTA: pvq_vector
+//   phase C  warp per band: walk the band's nodes in reverse (children before parents):
+//            normalise leaves, recombine mid/side, then apply the gain
+// Offsets in DNode are absolute positions in the CTA's ping-pong workspaces wsA / wsB.
+struct DNode {
+    unsigned long long u;      // leaf: Fischer index; internal: theta (double bits)
+    int K;                     // leaf: pulses
+    short off, n, prev;        // workspace offset, length, previous node of the same band (-1: none)
+    unsigned char capLog2, flags;
+};
+enum { DN_LEAF = 1, DN_ROOT = 2, DN_BUF = 4 };
+
+struct BandDec {               // per band, written by phase A (lane 0), read by phase C
+    double gain;
+    int tail;                  // last node appended (-1: no shape bits, shape = ones)
+    int L;
+};
+
+struct ParseNode { short off, cap, n, buf; int bits; short root; };
+
+__device__ __forceinline__ int dn_append(DNode* nodes, int* nNodes, int maxNodes, const DNode& nd, int* err) {
+    const int lane = threadIdx.x & 31;
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(nNodes, 1);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot >= maxNodes) { *err |= PVQ_ERR_STACK; return -1; }
+    if (lane == 0) nodes[slot] = nd;
+    return slot;
+}
+
+// Phase A for one band on one warp.  base = offset of the band's region (capacity cap, a power of
+// two >= L) in the workspaces.  All lanes hold the same cursor and run the scalar logic redundantly.
+__device__ __forceinline__ void warp_parse_gain_shape(const PvqTab& t, BitR& br, int R, int L, double* wsA, double* wsB,
+                                                      int base, int cap, DNode* nodes, int* nNodes, int maxNodes,
+                                                      BandDec* bd, int* err) {
+    const int lane = threadIdx.x & 31;
+    int bg, bs, tail = -1;
+    gs_alloc(t, R, L, &bg, &bs);
+    if (bs != 0) {
+        ParseNode st[24];
+        int sp = 0, used = 0;
+        st[sp++] = {(short)base, (short)cap, (short)L, 0, bs, 1};
+        while (sp > 0) {
+            const ParseNode nd = st[--sp];
+            DNode dn;
+            dn.off = nd.off; dn.n = nd.n; dn.prev = (short)tail;
+            dn.capLog2 = (unsigned char)(31 - __clz((int)nd.cap));
+            dn.flags = (unsigned char)((nd.buf ? DN_BUF : 0) | (nd.root ? DN_ROOT : 0));
+            if (nd.bits <= PVQ_SPLIT_BITS) {
+                long long K;
+                int w;
+                pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+                dn.u = br_get(br, w);
+                dn.K = (int)K;
+                dn.flags |= DN_LEAF;
+                used += w;
+                tail = dn_append(nodes, nNodes, maxNodes, dn, err);
+                if (tail < 0) break;
+                continue;
+            }
+            const int half = (nd.n + 1) / 2, hc = nd.cap / 2;
+            int aT, aMs, aMid, aSide;
+            gs_alloc(t, nd.bits, half, &aT, &aMs);
+            if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+            const unsigned long long ti = br_get(br, aT);
+            used += aT;
+            const double theta = dequantize_uniform(ti, aT) * 1.5707963267948966;
+            ms_alloc(aMs, theta, half, &aMid, &aSide);
+            double* oth = (nd.buf ? wsA : wsB) + nd.off;
+            for (int i = lane; i < half; i += 32) {       // children that get no bits stay zero
+                if (aMid <= 0) oth[i] = 0.0;
+                if (aSide <= 0) oth[hc + i] = 0.0;
+            }
+            dn.u = (unsigned long long)__double_as_longlong(theta);
+            dn.K = 0;
+            tail = dn_append(nodes, nNodes, maxNodes, dn, err);
+            if (tail < 0) break;
+            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
+            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, 0};
+            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid, 0};
+        }
+        bg += bs - used;
+    }
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    if (bg < 0) bg = 0;
+    const unsigned long long gi = br_get(br, bg);
+    const double gq = dequantize_uniform(gi, bg);
+    const double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
+    if (lane == 0) {
+        bd->gain = sg / 255.0 * (pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
+        bd->tail = tail;
+        bd->L = L;
+    }
+}
+
+// Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...
+__device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, const DNode* nodes, int nNodes, double* wsA,
+                                                  double* wsB, int tid, int nThreads, int* err) {
+    for (int i = tid; i < nNodes; i += nThreads) {
+        const DNode nd = nodes[i];
+        if (!(nd.flags & DN_LEAF)) continue;
+        int werr = 0;
+        pvq_vector(t, nd.u, nd.n, nd.K, ((nd.flags & DN_BUF) ? wsB : wsA) + nd.off, &werr);
+        if (werr) atomicOr(err, werr);
+    }
+}
+
+// Phase C for one band on one warp: out[0..L) <- gain * shape.  base as in phase A.
+__device__ __forceinline__ void warp_finish_gain_shape(const DNode* nodes, const BandDec& bd, double* wsA, double* wsB,
+                                                       int base, double* out) {
+    const int lane = threadIdx.x & 31;
+    const int L = bd.L;
+    if (bd.tail < 0) {
+        for (int i = lane; i < L; i += 32) out[i] = bd.gain;                 // shape = ones
+        return;
+    }
+    for (int idx = bd.tail; idx >= 0;) {
+        const DNode nd = nodes[idx];
+        idx = nd.prev;
+        double* cur = ((nd.flags & DN_BUF) ? wsB : wsA) + nd.off;
+        double* oth = ((nd.flags & DN_BUF) ? wsA : wsB) + nd.off;
+        const int n = nd.n;
+        if (nd.flags & DN_LEAF) {
+            const int reps = (nd.flags & DN_ROOT) ? 2 : 1;                   // a root leaf is normalised twice
+            for (int r = 0; r < reps; ++r) {
+                double ss = 0.0;
+                for (int i = lane; i < n; i += 32) ss += cur[i] * cur[i];
+                const double nr = sqrt(warp_sum(ss));
+                if (nr != 0.0)
+                    for (int i = lane; i < n; i += 32) cur[i] = cur[i] / nr;
+                __syncwarp();
+            }
+            continue;
+        }
+        // recombine (coder/gain_shape_quantize.py:449-463)
+        const int mid = n / 2, half = (n + 1) / 2, hc = (1 << nd.capLog2) / 2;
+        const double theta = __longlong_as_double((long long)nd.u);
+        const double ct = cos(theta), sn = sin(theta), r2 = sqrt(2.0);
+        double ss = 0.0;
+        for (int i = lane; i < half; i += 32) {
+            const double m = oth[i], s = oth[hc + i];
+            const double l = (m * ct + s * sn) / r2;
+            const double r = (m * ct - s * sn) / r2;
+            if (i < mid) { cur[i] = l; ss += l * l; }      // odd n: the padded last element of left is dropped
+            cur[mid + i] = r;
+            ss += r * r;
+        }
+        const double nr = sqrt(warp_sum(ss));
+        __syncwarp();
+        if (nr != 0.0)
+            for (int i = lane; i < n; i += 32) cur[i] = cur[i] / nr;
+        __syncwarp();
+    }
+    for (int i = lane; i < L; i += 32) out[i] = bd.gain * wsA[base + i];
+    __syncwarp();
+}
