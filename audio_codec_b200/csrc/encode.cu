@@ -102,26 +102,7 @@ __global__ void __launch_bounds__(ENC_NT)
 k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EncSmem S;
-    double* dp = reinterpret_cast<double*>(smem_raw);
-    S.xs = dp; dp += 2048;
-    S.fb = dp; dp += 2048;
-    S.lines = dp; dp += 1024;
-    S.mk = dp; dp += 1040;
-    S.smr = dp; dp += 32;
-    S.tmp = dp; dp += 32;
-    S.red = dp; dp += 16;
-    S.env = dp; dp += 32;
-    unsigned* up = reinterpret_cast<unsigned*>(dp);
-    S.blockbuf = up; up += REC_WORDS;
-    S.bandbits = up; up += BAND_WORDS;
-    int* ip = reinterpret_cast<int*>(up);
-    S.ba = ip; ip += 32;
-    S.nlEff = ip; ip += 32;
-    S.used = ip; ip += 32;
-    S.wordOff = ip; ip += 34;
-    S.capOff = ip; ip += 34;
-    S.sfb = ip; ip += 32;
-    S.misc = ip; ip += 16;
+    enc_smem_carve(smem_raw, S);
     S.logVal = nullptr; S.logW = nullptr; S.logCnt = nullptr; S.logCap = 0;
 
     const int tid = threadIdx.x;
@@ -353,8 +334,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     EncArgs a;
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
-    size_t smem = (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
-                  (REC_WORDS + BAND_WORDS) * sizeof(unsigned) + (32 * 4 + 34 * 2 + 16) * sizeof(int);
+    size_t smem = enc_smem_bytes();
     PAC_CHECK(cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaEventRecord(ctx->ev[0], st);
     k_encode<<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);

@@ -13,6 +13,7 @@
 #define REC_STRIDE 2176          // bytes per channel-block scratch record (>= worst-case declared size)
 #define REC_WORDS (REC_STRIDE / 4)
 #define BAND_WORDS 640
+#define ENC_MAX_LEAVES 640       // PVQ leaves per frame (a 128 kb/s long frame has ~100)
 
 // int16 PCM -> signed fraction (coder/pcmfile.py:89-98): 2|c|/65535 with the sign
 // restored; -32768 has magnitude bits 0 and maps to 0.0.
@@ -47,7 +48,39 @@ struct EncSmem {
     int* logW;
     int* logCnt;       // [nBands]
     int logCap;
+    ELeaf* leaves;     // [ENC_MAX_LEAVES] PVQ leaves of the current frame (phase A -> phase B)
 };
+
+__host__ __device__ constexpr size_t enc_smem_bytes() {
+    return (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
+           (REC_WORDS + BAND_WORDS) * sizeof(unsigned) + (32 * 4 + 34 * 2 + 16) * sizeof(int) +
+           ENC_MAX_LEAVES * sizeof(ELeaf);
+}
+
+__device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
+    double* dp = reinterpret_cast<double*>(raw);
+    S.xs = dp; dp += 2048;
+    S.fb = dp; dp += 2048;
+    S.lines = dp; dp += 1024;
+    S.mk = dp; dp += 1040;
+    S.smr = dp; dp += 32;
+    S.tmp = dp; dp += 32;
+    S.red = dp; dp += 16;
+    S.env = dp; dp += 32;
+    unsigned* up = reinterpret_cast<unsigned*>(dp);
+    S.blockbuf = up; up += REC_WORDS;
+    S.bandbits = up; up += BAND_WORDS;
+    int* ip = reinterpret_cast<int*>(up);
+    S.ba = ip; ip += 32;
+    S.nlEff = ip; ip += 32;
+    S.used = ip; ip += 32;
+    S.wordOff = ip; ip += 34;
+    S.capOff = ip; ip += 34;
+    S.sfb = ip; ip += 32;
+    S.misc = ip; ip += 16;
+    S.leaves = reinterpret_cast<ELeaf*>(ip);
+    S.logVal = nullptr; S.logW = nullptr; S.logCnt = nullptr; S.logCap = 0;
+}
 
 __device__ __forceinline__ double block_max(double v, double* red, int tid) {
 #pragma unroll
@@ -168,11 +201,13 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     double* wsA = (N == PAC_NLONG) ? S.xs : S.lines + 256;
     double* wsB = (N == PAC_NLONG) ? S.fb : S.lines + 512;
     if (dev->useVQ) {
+        // phase A: one warp per band builds the split tree, writes theta / gain fields, lists the leaves
+        if (tid == 0) S.misc[6] = 0;
+        __syncthreads();
         for (int b = warp; b < nB; b += ENC_NT / 32) {
             int used = 0;
             if (S.ba[b]) {
                 const int cap = S.capOff[b + 1] - S.capOff[b];
-                BitW bw = {S.bandbits + S.wordOff[b], 0};
                 int werr = 0;
                 FieldLog flog = {S.logVal + (size_t)b * S.logCap, S.logW + (size_t)b * S.logCap, S.logCnt + b, S.logCap};
                 FieldLog* lg = S.logVal ? &flog : nullptr;
@@ -181,12 +216,12 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
                     __shared__ double s_env[ENC_NT / 32];
                     if (lane == 0) s_env[warp] = (S.env[b] * up) / (double)bands.nLines[b];
                     __syncwarp();
-                    used = warp_quantize_gain_shape(pt, &s_env[warp], 1, S.ba[b], wsA + S.capOff[b],
-                                                    wsB + S.capOff[b], yws + S.capOff[b], cap, bw, &werr, lg);
+                    used = warp_plan_gain_shape(pt, &s_env[warp], 1, S.ba[b], wsA, wsB, S.capOff[b], cap, S.bandbits,
+                                                S.wordOff[b] * 32, b, S.leaves, &S.misc[6], ENC_MAX_LEAVES, &werr, lg);
                 } else {
-                    used = warp_quantize_gain_shape(pt, S.lines + bands.lower[b], bands.nLines[b],
-                                                    S.ba[b] * bands.nLines[b], wsA + S.capOff[b],
-                                                    wsB + S.capOff[b], yws + S.capOff[b], cap, bw, &werr, lg);
+                    used = warp_plan_gain_shape(pt, S.lines + bands.lower[b], bands.nLines[b], S.ba[b] * bands.nLines[b],
+                                                wsA, wsB, S.capOff[b], cap, S.bandbits, S.wordOff[b] * 32, b, S.leaves,
+                                                &S.misc[6], ENC_MAX_LEAVES, &werr, lg);
                 }
                 if (werr && lane == 0) atomicOr(err, werr);
             }
@@ -195,6 +230,10 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
                 if (used == 0) S.ba[b] = 0;               // coder/codec.py:352-353
             }
         }
+        __syncthreads();
+        // phase B: one thread per leaf: pulse search + Fischer index
+        cta_quantize_leaves(pt, S.leaves, min(S.misc[6], ENC_MAX_LEAVES), wsA, wsB, yws, S.bandbits, S.logVal, S.logCap,
+                            tid, ENC_NT, err);
     } else {
         for (int b = warp; b < nB; b += ENC_NT / 32) {
             const int lo = bands.lower[b], n = bands.nLines[b], bb = S.ba[b];

@@ -558,26 +558,7 @@ __global__ void __launch_bounds__(ENC_NT)
 k_encode_frames(const PacDev* __restrict__ dev, FrameEncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EncSmem S;
-    double* dp = reinterpret_cast<double*>(smem_raw);
-    S.xs = dp; dp += 2048;
-    S.fb = dp; dp += 2048;
-    S.lines = dp; dp += 1024;
-    S.mk = dp; dp += 1040;
-    S.smr = dp; dp += 32;
-    S.tmp = dp; dp += 32;
-    S.red = dp; dp += 16;
-    S.env = dp; dp += 32;
-    unsigned* up = reinterpret_cast<unsigned*>(dp);
-    S.blockbuf = up; up += REC_WORDS;
-    S.bandbits = up; up += BAND_WORDS;
-    int* ip = reinterpret_cast<int*>(up);
-    S.ba = ip; ip += 32;
-    S.nlEff = ip; ip += 32;
-    S.used = ip; ip += 32;
-    S.wordOff = ip; ip += 34;
-    S.capOff = ip; ip += 34;
-    S.sfb = ip; ip += 32;
-    S.misc = ip; ip += 16;
+    enc_smem_carve(smem_raw, S);
     const int tid = threadIdx.x;
     const long long f = blockIdx.x;
     const bool last = a.flags[f] & 1, cur = (a.flags[f] >> 1) & 1, nxt = (a.flags[f] >> 2) & 1;
@@ -649,10 +630,6 @@ k_encode_frames(const PacDev* __restrict__ dev, FrameEncArgs a) {
 
 extern "C" int pac_record_stride(void) { return REC_STRIDE; }
 
-static size_t enc_smem_bytes() {
-    return (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
-           (REC_WORDS + BAND_WORDS) * sizeof(unsigned) + (32 * 4 + 34 * 2 + 16) * sizeof(int);
-}
 
 static int run_encode_frames(pac_ctx* ctx, FrameEncArgs& a, long long n, int* h_err, cudaStream_t st) {
     void* scr = nullptr;

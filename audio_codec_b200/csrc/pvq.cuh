@@ -266,3 +266,214 @@ __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const d
     __syncwarp();
     return total + bg;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Two-phase form of quantize_gain_shape for the fused frame encoder.  The split tree (theta
+// fields, bit allocations, leaf sizes and therefore every field position) does not depend on the
+// pulse search, so:
+//   phase A  warp per band: build the tree top-down, write the theta and gain fields, append one
+//            ELeaf per PVQ leaf to a CTA-wide list (its K, field width and bit position are known)
+//   phase B  thread per leaf, all threads of the CTA: pulse search + Fischer index
+struct ELeaf {
+    short off, n;              // absolute workspace offset, length
+    int K;
+    int pos;                   // absolute bit position in the CTA's band bit buffers
+    unsigned char buf, w, band, pad;
+    short logSlot, pad2;
+};
+
+// np.add.reduce of |a[i]| in NumPy's pairwise order (loops_utils.h.src pairwise_sum): blocks of at
+// most 128 elements are summed with 8 accumulators, larger arrays are halved recursively.
+__device__ __forceinline__ double np_abs_sum_block(const double* a, int n) {
+    if (n < 8) {
+        double r = 0.0;
+        for (int i = 0; i < n; ++i) r += fabs(a[i]);
+        return r;
+    }
+    double r[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = fabs(a[j]);
+    int i;
+    for (i = 8; i < n - (n % 8); i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] += fabs(a[i + j]);
+    }
+    double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+    for (; i < n; ++i) res += fabs(a[i]);
+    return res;
+}
+__device__ __forceinline__ double np_abs_sum(const double* a, int n) {
+    if (n <= 128) return np_abs_sum_block(a, n);
+    // explicit post-order walk of the halving tree (depth <= 4 for n <= 1024)
+    struct Fr { const double* p; int n; int state; double left; };
+    Fr st[8];
+    int sp = 0;
+    st[sp++] = {a, n, 0, 0.0};
+    double ret = 0.0;
+    while (sp > 0) {
+        Fr& f = st[sp - 1];
+        if (f.n <= 128) { ret = np_abs_sum_block(f.p, f.n); --sp; continue; }
+        int n2 = f.n / 2;
+        n2 -= n2 % 8;
+        if (f.state == 0) { f.state = 1; st[sp++] = {f.p, n2, 0, 0.0}; continue; }
+        if (f.state == 1) { f.left = ret; f.state = 2; st[sp++] = {f.p + n2, f.n - n2, 0, 0.0}; continue; }
+        ret = f.left + ret;
+        --sp;
+    }
+    return ret;
+}
+
+// quantize_pvq for one leaf on ONE thread (coder/gain_shape_quantize.py:41-54, :105-124).
+__device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& t, const double* vec, double* res, int* y,
+                                                                  int n, long long K, int* err) {
+    if (K == 0) return 0ull;
+    const double l1 = np_abs_sum(vec, n);
+    if (l1 == 0.0) { *err |= PVQ_ERR_DEGENERATE; return 0ull; }
+    long long ps = 0;
+    for (int i = 0; i < n; ++i) {
+        double xh = fabs(((double)K * vec[i]) / l1);
+        double p = floor(xh);
+        res[i] = xh - p;
+        y[i] = (int)p;
+        ps += (long long)p;
+    }
+    for (long long rem = K - ps; rem > 0; --rem) {        // np.argmax: first maximum
+        double bv = res[0];
+        int bi = 0;
+        for (int i = 1; i < n; ++i) {
+            double r = res[i];
+            if (r > bv) { bv = r; bi = i; }
+        }
+        res[bi] -= 1.0;
+        y[bi] += 1;
+    }
+    unsigned long long acc = 0ull;
+    long long k = K;
+    for (int i = 0; i < n && k > 0; ++i) {
+        const int a = y[i];
+        if (a > 0) {
+            const int l = n - i;
+            const unsigned long long below = pvq_N(t, l - 1, k - a);
+            unsigned long long c = pvq_N(t, l, k) - pvq_N(t, l, k - a) - below;
+            if (vec[i] < 0.0) c += below;
+            acc += c;
+            k -= a;
+        }
+    }
+    return acc;
+}
+
+// Phase A for one band on one warp.  x[0..L): band lines (shared); base/cap: the band's region in
+// the ping-pong workspaces wsA / wsB; words: the CTA's band bit buffers (zero-initialised), bit0:
+// first bit of this band's private buffer.  Returns the bits the band emits (0: all-zero band).
+__device__ __forceinline__ int warp_plan_gain_shape(const PvqTab& t, const double* x, int L, int R, double* wsA,
+                                                    double* wsB, int base, int cap, unsigned* words, int bit0, int band,
+                                                    ELeaf* leaves, int* nLeaves, int maxLeaves, int* err,
+                                                    FieldLog* lg = nullptr) {
+    const int lane = threadIdx.x & 31;
+    int bg, bs;
+    gs_alloc(t, R, L, &bg, &bs);
+    double ss = 0.0;
+    for (int i = lane; i < L; i += 32) ss += x[i] * x[i];
+    const double gain = sqrt(warp_sum(ss));
+    if (gain == 0.0) return 0;
+    int pos = bit0;                                     // lane-uniform write cursor
+    auto put = [&](unsigned long long v, int n) {       // fields written in phase A: theta, gain
+        if (lane == 0) {
+            BitW bw = {words, pos};
+            bw_put(bw, v, n);
+            log_field(lg, v, n);
+        }
+        pos += n;
+    };
+    if (bs != 0) {
+        for (int i = lane; i < L; i += 32) wsA[base + i] = x[i] / gain;
+        __syncwarp();
+        PvqNode st[24];
+        int sp = 0;
+        st[sp++] = {(short)base, (short)cap, (short)L, 0, bs};
+        while (sp > 0) {
+            const PvqNode nd = st[--sp];
+            double* cur = (nd.buf ? wsB : wsA) + nd.off;
+            double* oth = (nd.buf ? wsA : wsB) + nd.off;
+            if (nd.bits <= PVQ_SPLIT_BITS) {
+                long long K;
+                int w;
+                pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+                if (K > 0) {
+                    int slot = 0, ls = -1;
+                    if (lane == 0) {
+                        slot = atomicAdd(nLeaves, 1);
+                        if (lg) { ls = *lg->count; log_field(lg, 0ull, w); }
+                        if (slot < maxLeaves) {
+                            ELeaf lf;
+                            lf.off = nd.off; lf.n = nd.n; lf.K = (int)K; lf.pos = pos;
+                            lf.buf = (unsigned char)nd.buf; lf.w = (unsigned char)w; lf.band = (unsigned char)band; lf.pad = 0;
+                            lf.logSlot = (short)ls; lf.pad2 = 0;
+                            leaves[slot] = lf;
+                        }
+                    }
+                    slot = __shfl_sync(0xffffffffu, slot, 0);
+                    if (slot >= maxLeaves) { *err |= PVQ_ERR_STACK; break; }
+                    pos += w;
+                } else {
+                    put(0ull, w);                      // empty leaf: index 0 in a 1-bit field
+                }
+                continue;
+            }
+            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+            double sm = 0.0, sd = 0.0;
+            for (int i = lane; i < half; i += 32) {
+                double l = i < mid ? cur[i] : 0.0;       // odd n: the LEFT half is zero padded at its end
+                double r = cur[mid + i];
+                double M = (l + r) / 2.0, S = (l - r) / 2.0;
+                oth[i] = M;
+                oth[hc + i] = S;
+                sm += M * M;
+                sd += S * S;
+            }
+            const double nm = sqrt(warp_sum(sm)), ns = sqrt(warp_sum(sd));
+            __syncwarp();
+            for (int i = lane; i < half; i += 32) {
+                if (nm != 0.0) oth[i] = oth[i] / nm;
+                if (ns != 0.0) oth[hc + i] = oth[hc + i] / ns;
+            }
+            __syncwarp();
+            const double theta = nm == 0.0 ? 0.0 : atan(ns / nm);
+            int aT, aMs, aMid, aSide;
+            gs_alloc(t, nd.bits, half, &aT, &aMs);
+            const double hp = 1.5707963267948966;        // np.pi / 2
+            if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+            const unsigned long long ti = quantize_uniform(theta / hp, aT);
+            const double tq = dequantize_uniform(ti, aT) * hp;
+            ms_alloc(aMs, tq, half, &aMid, &aSide);
+            put(ti, aT);
+            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
+            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide};
+            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid};
+        }
+        bg += bs - (pos - bit0);
+    }
+    const double g = log(1.0 + 255.0 * (gain / (double)L)) / log(256.0);      // mu_law_fn
+    if (bg < 0) bg = 0;
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    put(quantize_uniform(g, bg), bg);
+    __syncwarp();
+    return pos - bit0;
+}
+
+// Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...  yws: int workspace
+// indexed like wsA / wsB.  logVal/logCap: the frame's field log ([band][logCap]) or nullptr.
+__device__ __forceinline__ void cta_quantize_leaves(const PvqTab& t, const ELeaf* leaves, int nLeaves, double* wsA,
+                                                    double* wsB, int* yws, unsigned* words, unsigned long long* logVal,
+                                                    int logCap, int tid, int nThreads, int* err) {
+    for (int i = tid; i < nLeaves; i += nThreads) {
+        const ELeaf lf = leaves[i];
+        int werr = 0;
+        const unsigned long long idx = thread_quantize_pvq(t, (lf.buf ? wsB : wsA) + lf.off, (lf.buf ? wsA : wsB) + lf.off,
+                                                           yws + lf.off, lf.n, lf.K, &werr);
+        bw_put_at(words, lf.pos, idx, lf.w);
+        if (logVal && lf.logSlot >= 0 && lf.logSlot < logCap) logVal[(size_t)lf.band * logCap + lf.logSlot] = idx;
+        if (werr) atomicOr(err, werr);
+    }
+}
