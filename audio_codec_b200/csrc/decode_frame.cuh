@@ -104,7 +104,7 @@ __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, l
     const int scale = S.misc[5];
     // (2) bands: VQ in three phases (parse per band / index decode per leaf / recombine per band),
     //     block floating point directly
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab};
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
     const int omPos = dev->sbrCutoff;
     if (dev->useVQ) {
         for (int b = warp; b < nB; b += DEC_NT / 32) {

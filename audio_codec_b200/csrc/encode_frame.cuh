@@ -194,7 +194,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     for (int i = tid; i < BAND_WORDS; i += ENC_NT) S.bandbits[i] = 0u;
     __syncthreads();
     if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (N == PAC_NLONG ? 2048 : 256)) return 0;
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab};
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
     int* yws = reinterpret_cast<int*>(S.mk);              // masked threshold is dead from here on
     // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
     // sub-frame must leave xs intact for its siblings and uses the tail of lines[]

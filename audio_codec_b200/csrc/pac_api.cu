@@ -254,6 +254,36 @@ static int make_pvq(pac_ctx* c) {
     int rc;
     std::vector<double> lg(PAC_PVQ_LMAX + 1, 0.0);
     for (int L = 1; L <= PAC_PVQ_LMAX; ++L) lg[L] = (double)log2l((long double)L);
+    {   // K(L, bits): largest K with N(L,K) <= 2^bits, and ceil(log2 N(L,K)) with the 1-bit minimum
+        // (coder/gain_shape_quantize.py:275-291)
+        std::vector<int2> kw((size_t)(PAC_PVQ_LMAX + 1) * 33);
+        auto NLK = [&](int L, unsigned long long k) -> unsigned long long {
+            if (k == 0) return 1ull;
+            if (L <= 0) return 0ull;
+            if (L == 1) return 2ull;
+            if (L == 2) return 4ull * k;
+            if (L == 3) return 4ull * k * k + 2ull;
+            size_t o = off[L], len = off[L + 1] - off[L];
+            return k >= len ? (1ull << 40) : all[o + k];
+        };
+        for (int L = 0; L <= PAC_PVQ_LMAX; ++L)
+            for (int b = 0; b <= 32; ++b) {
+                unsigned long long lim = 1ull << b, k = 0;
+                if (L == 2) k = lim / 4ull;
+                else if (L == 3) { while (NLK(3, k + 1) <= lim) ++k; }
+                else if (L >= 4) {
+                    size_t o = off[L], len = off[L + 1] - off[L];
+                    size_t lo = 0, hi = len;
+                    while (lo < hi) { size_t mid = (lo + hi) / 2; if (all[o + mid] > lim) hi = mid; else lo = mid + 1; }
+                    k = lo - 1;
+                }
+                unsigned long long n = NLK(L, k);
+                int w = 1;
+                if (n > 1) { w = 0; unsigned long long v = n - 1; while (v) { ++w; v >>= 1; } }
+                kw[(size_t)L * 33 + b] = make_int2((int)k, w);
+            }
+        if ((rc = upload(c, kw, &c->host.pvqKW))) return rc;
+    }
     if ((rc = upload(c, lg, &c->host.log2tab))) return rc;
     if ((rc = upload(c, all, &c->host.pvqN))) return rc;
     return upload(c, off, &c->host.pvqRowOff);

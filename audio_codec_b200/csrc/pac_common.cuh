@@ -69,6 +69,8 @@ struct PacDev {
     const unsigned long long* pvqN;
     const int* pvqRowOff;      // [PAC_PVQ_LMAX+2]
     const double* log2tab;     // [PAC_PVQ_LMAX+1] log2(L) (entry 0 unused)
+    // pvq_compute_k_for_R as a table: [(PAC_PVQ_LMAX+1)][33] of {K, field width} for bits = 0..32
+    const int2* pvqKW;
     // SBR decode: response of gaussian_filter1d(sigma=200, reflect) to unit impulses
     const double* sbrGauss;    // [nOmitted][2*(1024-cutoff)] (only first half used)
     int sbrNOmitted;

@@ -16,6 +16,7 @@ struct PvqTab {
     const unsigned long long* N;
     const int* off;
     const double* log2tab;   // log2(L), L <= PAC_PVQ_LMAX
+    const int2* KW;          // {K, width}[L][bits], bits 0..32
 };
 
 // N(l,k): rows 0..3 closed form, others from the table; entries past a row's end
@@ -34,33 +35,10 @@ __device__ __forceinline__ unsigned long long pvq_N(const PvqTab& t, int l, long
 // pvq_compute_k_for_R: largest K with N(L,K) <= 2^bits, and the field width
 // ceil(log2(N(L,K) + eps)) -- which is 1 (not 0) for N == 1.  bits <= 32.
 __device__ __forceinline__ void pvq_k_for_bits(const PvqTab& t, int L, int bits, long long* K, int* used, int* err) {
-    unsigned long long lim = 1ull << bits;
-    long long k = 0;
-    if (L <= 1) {
-        if (bits >= 1) *err |= PVQ_ERR_DEGENERATE;      // the reference never terminates here
-        k = 0;
-    } else if (L == 2) {
-        k = (long long)(lim / 4ull);
-    } else if (L == 3) {
-        if (lim >= 6ull) {
-            unsigned long long q = (lim - 2ull) / 4ull;
-            long long r = (long long)sqrt((double)q);
-            while ((unsigned long long)(r + 1) * (unsigned long long)(r + 1) <= q) ++r;
-            while ((unsigned long long)r * (unsigned long long)r > q) --r;
-            k = r;
-        }
-    } else {
-        int o = t.off[L], len = t.off[L + 1] - o;       // row is ascending; last entry > 2^32
-        int lo = 0, hi = len;                            // first index with N > lim
-        while (lo < hi) {
-            int mid = (lo + hi) >> 1;
-            if (t.N[o + mid] > lim) hi = mid; else lo = mid + 1;
-        }
-        k = lo - 1;
-    }
-    unsigned long long n = pvq_N(t, L, k);
-    *K = k;
-    *used = n <= 1ull ? 1 : 64 - __clzll((long long)(n - 1ull));
+    if (L <= 1 && bits >= 1) *err |= PVQ_ERR_DEGENERATE;      // the reference never terminates here
+    const int2 kw = t.KW[L * 33 + bits];
+    *K = kw.x;
+    *used = kw.y;
 }
 
 // gain_shape_alloc(R, L, 0): coder/gain_shape_quantize.py:57-62
@@ -467,7 +445,10 @@ __device__ __forceinline__ int warp_plan_gain_shape(const PvqTab& t, const doubl
 __device__ __forceinline__ void cta_quantize_leaves(const PvqTab& t, const ELeaf* leaves, int nLeaves, double* wsA,
                                                     double* wsB, int* yws, unsigned* words, unsigned long long* logVal,
                                                     int logCap, int tid, int nThreads, int* err) {
-    for (int i = tid; i < nLeaves; i += nThreads) {
+    // leaf j goes to warp j % nWarps, lane j / nWarps: the serial per-leaf walks diverge, so spread
+    // them over all warps (and schedulers) instead of filling a few warps
+    const int nWarps = nThreads >> 5;
+    for (int i = (tid & 31) * nWarps + (tid >> 5); i < nLeaves; i += nThreads) {
         const ELeaf lf = leaves[i];
         int werr = 0;
         const unsigned long long idx = thread_quantize_pvq(t, (lf.buf ? wsB : wsA) + lf.off, (lf.buf ? wsA : wsB) + lf.off,

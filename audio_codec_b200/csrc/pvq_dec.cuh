@@ -242,7 +242,8 @@ __device__ __forceinline__ void warp_parse_gain_shape(const PvqTab& t, BitR& br,
 // Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...
 __device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, const DNode* nodes, int nNodes, double* wsA,
                                                   double* wsB, int tid, int nThreads, int* err) {
-    for (int i = tid; i < nNodes; i += nThreads) {
+    const int nWarps = nThreads >> 5;                      // node j -> warp j % nWarps, lane j / nWarps
+    for (int i = (tid & 31) * nWarps + (tid >> 5); i < nNodes; i += nThreads) {
         const DNode nd = nodes[i];
         if (!(nd.flags & DN_LEAF)) continue;
         int werr = 0;
