@@ -150,12 +150,9 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     __syncthreads();
 
     // (3) psychoacoustic model -> SMR per band
-    double* mz = S.fb;
-    double* ms = S.fb + 640;
-    double* mkk = S.fb + 1280;
-    pick_maskers<N, ENC_NT>(S.mk, pc, mz, ms, mkk, &S.misc[0], tid);
-    const int nMask = S.misc[0];
-    masked_threshold<N, ENC_NT>(pc, mz, ms, mkk, nMask, S.mk, tid);
+    const MaskerList ml = masker_list(S.fb);
+    const int nMask = pick_maskers<N, ENC_NT>(S.mk, pc, ml, tid);
+    masked_threshold<N, ENC_NT>(pc, ml, nMask, S.mk, tid);
     band_smr<ENC_NT>(S.lines, scale, S.mk, bands, S.smr, tid);
 
     // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)

@@ -112,7 +112,6 @@ k_calc_smr(const PacDev* __restrict__ dev, const double* __restrict__ data, cons
     double* mk = fb + (N > 1920 ? N : 1920);              // [H + 16]
     double* lines = mk + H + 16;                          // [H]
     double* smrS = lines + H;                             // [32]
-    __shared__ int s_cnt;
     const int tid = threadIdx.x;
     const long long f = blockIdx.x;
     const PsyConst pc = psy_const<N>(dev);
@@ -125,11 +124,9 @@ k_calc_smr(const PacDev* __restrict__ dev, const double* __restrict__ data, cons
         mk[k] = pc.norm * (m * m);
     }
     __syncthreads();
-    double* mz = fb;
-    double* ms = fb + 640;
-    double* mkk = fb + 1280;
-    pick_maskers<N, ENC_NT>(mk, pc, mz, ms, mkk, &s_cnt, tid);
-    masked_threshold<N, ENC_NT>(pc, mz, ms, mkk, s_cnt, mk, tid);
+    const MaskerList ml = masker_list(fb);
+    const int nMask = pick_maskers<N, ENC_NT>(mk, pc, ml, tid);
+    masked_threshold<N, ENC_NT>(pc, ml, nMask, mk, tid);
     if (maskOut) for (int i = tid; i < H; i += ENC_NT) maskOut[f * H + i] = mk[i];
     if (smr) {
         band_smr<ENC_NT>(lines, scale[f], mk, bands, smrS, tid);
