@@ -8,7 +8,7 @@
 
 #define DEC_NT 256
 #define DEC_REC_MAX 4096          // largest channel-block payload accepted (bytes)
-#define DEC_MAX_NODES 896         // split-tree nodes per frame (a 128 kb/s long frame has ~150)
+#define DEC_MAX_NODES 512         // split-tree nodes per frame (a 128 kb/s long frame has ~150); sized for 3 CTAs per SM
 
 struct DecSmem {
     unsigned char* rec;   // [DEC_REC_MAX] payload bytes

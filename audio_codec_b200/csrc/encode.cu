@@ -98,7 +98,7 @@ struct EncArgs {
     int* err;              // [1] OR of soft error flags
 };
 
-__global__ void __launch_bounds__(ENC_NT)
+__global__ void __launch_bounds__(ENC_NT, 3)
 k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EncSmem S;
