@@ -14,6 +14,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--use_fast_math=false"]
 FLAGS = [f for f in FLAGS if f != "--use_fast_math=false"]  # never fast-math: fp64 parity path
+FLAGS += os.environ.get("PAC_CFLAGS", "").split()          # e.g. -DPAC_PHASE_TIMING (debug builds only)
 
 
 def sources():

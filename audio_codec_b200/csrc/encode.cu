@@ -358,3 +358,13 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     if (hOff[S] > out_capacity) return PAC_ERR_ARG;
     return hHdr[0] ? PAC_ERR_SOFT : 0;
 }
+
+#ifdef PAC_PHASE_TIMING
+// debug: copy and reset the per-phase cycle counters ([0..15] long frames, [16..31] short sub-frames)
+extern "C" int pac_debug_phases(unsigned long long* h_out) {
+    unsigned long long z[32] = {0};
+    cudaMemcpyFromSymbol(h_out, g_pac_phase, sizeof(z));
+    cudaMemcpyToSymbol(g_pac_phase, z, sizeof(z));
+    return 0;
+}
+#endif

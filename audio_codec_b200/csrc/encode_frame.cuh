@@ -10,10 +10,20 @@
 #include "pvq.cuh"
 
 #define ENC_NT 256
+
+// Optional per-phase cycle accounting (build with -DPAC_PHASE_TIMING; read with pac_debug_phases).
+#ifdef PAC_PHASE_TIMING
+static __device__ unsigned long long g_pac_phase[32];
+#define PHASE_T0() long long ph_t_ = clock64()
+#define PHASE(i) do { __syncthreads(); if (threadIdx.x == 0) { long long n_ = clock64(); atomicAdd(&g_pac_phase[(i) + (N == PAC_NLONG ? 0 : 16)], (unsigned long long)(n_ - ph_t_)); ph_t_ = n_; } } while (0)
+#else
+#define PHASE_T0()
+#define PHASE(i)
+#endif
 #define REC_STRIDE 2176          // bytes per channel-block scratch record (>= worst-case declared size)
 #define REC_WORDS (REC_STRIDE / 4)
 #define BAND_WORDS 640
-#define ENC_MAX_LEAVES 640       // PVQ leaves per frame (a 128 kb/s long frame has ~100)
+#define ENC_MAX_NODES 512        // split-tree nodes per frame (a 128 kb/s long frame has ~150)
 
 // int16 PCM -> signed fraction (coder/pcmfile.py:89-98): 2|c|/65535 with the sign
 // restored; -32768 has magnitude bits 0 and maps to 0.0.
@@ -48,13 +58,14 @@ struct EncSmem {
     int* logW;
     int* logCnt;       // [nBands]
     int logCap;
-    ELeaf* leaves;     // [ENC_MAX_LEAVES] PVQ leaves of the current frame (phase A -> phase B)
+    TNode* nodes;      // [ENC_MAX_NODES] split-tree nodes of the current frame
+    BandEnc* bandEnc;  // [32]
 };
 
 __host__ __device__ constexpr size_t enc_smem_bytes() {
     return (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
            (REC_WORDS + BAND_WORDS) * sizeof(unsigned) + (32 * 4 + 34 * 2 + 16) * sizeof(int) +
-           ENC_MAX_LEAVES * sizeof(ELeaf);
+           ENC_MAX_NODES * sizeof(TNode) + 32 * sizeof(BandEnc);
 }
 
 __device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
@@ -78,7 +89,8 @@ __device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
     S.capOff = ip; ip += 34;
     S.sfb = ip; ip += 32;
     S.misc = ip; ip += 16;
-    S.leaves = reinterpret_cast<ELeaf*>(ip);
+    S.nodes = reinterpret_cast<TNode*>(ip);
+    S.bandEnc = reinterpret_cast<BandEnc*>(S.nodes + ENC_MAX_NODES);
     S.logVal = nullptr; S.logW = nullptr; S.logCnt = nullptr; S.logCap = 0;
 }
 
@@ -113,6 +125,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     const cplx<double>* rootsQ = reinterpret_cast<const cplx<double>*>(dev->d.tw_fft[N == PAC_NLONG ? 2 : 0]);
     cplx<double>* fbuf = reinterpret_cast<cplx<double>*>(S.fb);
 
+    PHASE_T0();
     // (1) window + MDCT (coder/codec.py:301-305)
     mdct_fold<double, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
     __syncthreads();
@@ -123,6 +136,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     for (int i = tid; i < H; i += ENC_NT) mx = fmax(mx, fabs(S.lines[i]));
     double maxLine = block_max(mx, S.red, tid);
 
+    PHASE(0);
     // (2) Hann FFT magnitude (shared by the psychoacoustic model and the SBR envelope)
     hann_rfft_mag<N, ENC_NT>(fx, pc, fbuf, S.mk, tid);
     if (sbr) {                                    // coder/codec.py:460-473
@@ -149,12 +163,14 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     }
     __syncthreads();
 
+    PHASE(1);
     // (3) psychoacoustic model -> SMR per band
     const MaskerList ml = masker_list(S.fb);
     const int nMask = pick_maskers<N, ENC_NT>(S.mk, pc, ml, tid);
     masked_threshold<N, ENC_NT>(pc, ml, nMask, S.mk, tid);
     band_smr<ENC_NT>(S.lines, scale, S.mk, bands, S.smr, tid);
 
+    PHASE(2);
     // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)
     if (tid < nB) S.nlEff[tid] = (sbr && bands.omitted[tid]) ? 1 : bands.nLines[tid];
     __syncthreads();
@@ -172,6 +188,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     }
     __syncthreads();
 
+    PHASE(3);
     // (5) quantise each coded band into its private bit buffer
     if (tid == 0) {
         int w = 0, c = 0;
@@ -198,38 +215,78 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     double* wsA = (N == PAC_NLONG) ? S.xs : S.lines + 256;
     double* wsB = (N == PAC_NLONG) ? S.fb : S.lines + 512;
     if (dev->useVQ) {
-        // phase A: one warp per band builds the split tree, writes theta / gain fields, lists the leaves
+        // roots: one warp per band: gain, normalised copy of the band, root node of its split tree
         if (tid == 0) S.misc[6] = 0;
         __syncthreads();
         for (int b = warp; b < nB; b += ENC_NT / 32) {
-            int used = 0;
-            if (S.ba[b]) {
-                const int cap = S.capOff[b + 1] - S.capOff[b];
-                int werr = 0;
-                FieldLog flog = {S.logVal + (size_t)b * S.logCap, S.logW + (size_t)b * S.logCap, S.logCnt + b, S.logCap};
-                FieldLog* lg = S.logVal ? &flog : nullptr;
-                if (sbr && bands.omitted[b]) {
-                    // one value: mean |fftLines| of the band (coder/codec.py:508-510)
-                    __shared__ double s_env[ENC_NT / 32];
-                    if (lane == 0) s_env[warp] = (S.env[b] * up) / (double)bands.nLines[b];
-                    __syncwarp();
-                    used = warp_plan_gain_shape(pt, &s_env[warp], 1, S.ba[b], wsA, wsB, S.capOff[b], cap, S.bandbits,
-                                                S.wordOff[b] * 32, b, S.leaves, &S.misc[6], ENC_MAX_LEAVES, &werr, lg);
-                } else {
-                    used = warp_plan_gain_shape(pt, S.lines + bands.lower[b], bands.nLines[b], S.ba[b] * bands.nLines[b],
-                                                wsA, wsB, S.capOff[b], cap, S.bandbits, S.wordOff[b] * 32, b, S.leaves,
-                                                &S.misc[6], ENC_MAX_LEAVES, &werr, lg);
+            if (!S.ba[b]) continue;
+            const bool env = sbr && bands.omitted[b];       // one value: mean |fftLines| (coder/codec.py:508-510)
+            const int L = env ? 1 : bands.nLines[b], R = env ? S.ba[b] : S.ba[b] * bands.nLines[b];
+            const double* x = S.lines + bands.lower[b];
+            const double envVal = env ? (S.env[b] * up) / (double)bands.nLines[b] : 0.0;
+            int bg, bs;
+            gs_alloc(pt, R, L, &bg, &bs);
+            double ss = 0.0;
+            if (env) ss = lane == 0 ? envVal * envVal : 0.0;
+            else for (int i = lane; i < L; i += 32) ss += x[i] * x[i];
+            const double gain = sqrt(warp_sum(ss));
+            int root = -1;
+            if (gain != 0.0 && bs != 0) {
+                for (int i = lane; i < L; i += 32) wsA[S.capOff[b] + i] = (env ? envVal : x[i]) / gain;
+                if (lane == 0) {
+                    root = atomicAdd(&S.misc[6], 1);
+                    if (root < ENC_MAX_NODES) {
+                        TNode r;
+                        r.val = 0ull; r.bits = bs; r.K = -2; r.off = (short)S.capOff[b]; r.n = (short)L;
+                        r.kid[0] = r.kid[1] = -1;
+                        r.capLog2 = (unsigned char)(31 - __clz(S.capOff[b + 1] - S.capOff[b]));
+                        r.buf = 0; r.band = (unsigned char)b; r.w = 0; r.logSlot = -1; r.pad = 0;
+                        S.nodes[root] = r;
+                    } else {
+                        atomicOr(err, PVQ_ERR_STACK);
+                        root = -1;
+                    }
                 }
-                if (werr && lane == 0) atomicOr(err, werr);
             }
             if (lane == 0) {
-                S.used[b] = used;
-                if (used == 0) S.ba[b] = 0;               // coder/codec.py:352-353
+                BandEnc be;
+                be.gain = gain; be.bg = bg; be.bs = bs; be.root = root; be.L = L;
+                S.bandEnc[b] = be;
             }
         }
+        PHASE(4);
+        // levels: the nodes of one tree depth of all bands, spread over all warps
         __syncthreads();
-        // phase B: one thread per leaf: pulse search + Fischer index
-        cta_quantize_leaves(pt, S.leaves, min(S.misc[6], ENC_MAX_LEAVES), wsA, wsB, yws, S.bandbits, S.logVal, S.logCap,
+        for (int lvl0 = 0, lvl1 = min(S.misc[6], ENC_MAX_NODES); lvl0 < lvl1;) {
+            __syncthreads();                                // everyone has read the level bounds
+            for (int i = lvl0 + warp; i < lvl1; i += ENC_NT / 32) {
+                int werr = 0;
+                warp_plan_node(pt, S.nodes, i, &S.misc[6], ENC_MAX_NODES, wsA, wsB, &werr);
+                if (werr && lane == 0) atomicOr(err, werr);
+            }
+            __syncthreads();
+            lvl0 = lvl1;
+            lvl1 = min(S.misc[6], ENC_MAX_NODES);
+        }
+        __syncthreads();
+        // layout: one thread per band: field positions, theta and gain fields
+        if (tid < nB) {
+            const int b = tid;
+            int used = 0;
+            if (S.ba[b] && S.bandEnc[b].gain != 0.0) {
+                int werr = 0;
+                FieldLog flog = {S.logVal + (size_t)b * S.logCap, S.logW + (size_t)b * S.logCap, S.logCnt + b, S.logCap};
+                used = thread_layout_band(S.nodes, S.bandEnc[b], S.bandbits, S.wordOff[b] * 32, &werr,
+                                          S.logVal ? &flog : nullptr);
+                if (werr) atomicOr(err, werr);
+            }
+            S.used[b] = used;
+            if (used == 0) S.ba[b] = 0;                     // coder/codec.py:352-353
+        }
+        __syncthreads();
+        PHASE(5);
+        // leaves: one thread per leaf: pulse search + Fischer index
+        cta_quantize_leaves(pt, S.nodes, min(S.misc[6], ENC_MAX_NODES), wsA, wsB, yws, S.bandbits, S.logVal, S.logCap,
                             tid, ENC_NT, err);
     } else {
         for (int b = warp; b < nB; b += ENC_NT / 32) {
@@ -251,6 +308,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     }
     __syncthreads();
 
+    PHASE(6);
     // (6) frame header + band payload positions (coder/pacfile.py:363-447), thread 0
     if (tid == 0) {
         BitW bw = {S.blockbuf, *bpos};
@@ -274,6 +332,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
         S.misc[5] = scale;
     }
     __syncthreads();
+    PHASE(7);
     // (7) merge the band buffers into the block bitstream (disjoint bit ranges)
     for (int b = warp; b < nB; b += ENC_NT / 32) {
         const int u = S.ba[b] ? S.used[b] : 0;
@@ -284,6 +343,7 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
         }
     }
     __syncthreads();
+    PHASE(8);
     return S.misc[2];
 }
 

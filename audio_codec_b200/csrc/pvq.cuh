@@ -246,18 +246,30 @@ __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const d
 }
 
 // ---------------------------------------------------------------------------------------------
-// Two-phase form of quantize_gain_shape for the fused frame encoder.  The split tree (theta
-// fields, bit allocations, leaf sizes and therefore every field position) does not depend on the
-// pulse search, so:
-//   phase A  warp per band: build the tree top-down, write the theta and gain fields, append one
-//            ELeaf per PVQ leaf to a CTA-wide list (its K, field width and bit position are known)
-//   phase B  thread per leaf, all threads of the CTA: pulse search + Fischer index
-struct ELeaf {
+// Level-synchronous form of quantize_gain_shape for the fused frame encoder.  The split tree
+// (theta fields, bit allocations, leaf sizes, and therefore every field position) does not depend
+// on the pulse search, and the mid and side subtrees of a node are independent.  So, per frame:
+//   roots    warp per band: gain, normalised copy, root node
+//   levels   all warps: the nodes of one tree depth of ALL bands at a time (a node's children are
+//            appended to the pool, so each depth is a contiguous index range)
+//   layout   thread per band: pre-order walk -> bit position of every field, theta and gain
+//            fields written
+//   leaves   thread per leaf, all threads: pulse search + Fischer index
+struct TNode {                 // 32 bytes
+    unsigned long long val;    // internal: quantised theta
+    int bits;                  // shape bits given to the node; for a leaf, after layout: its bit position
+    int K;                     // -2 not yet visited, -1 internal, >= 0 leaf with K pulses
     short off, n;              // absolute workspace offset, length
-    int K;
-    int pos;                   // absolute bit position in the CTA's band bit buffers
-    unsigned char buf, w, band, pad;
-    short logSlot, pad2;
+    short kid[2];              // mid / side child (-1: none)
+    unsigned char capLog2, buf, band, w;    // w: field width (theta bits or index bits)
+    short logSlot, pad;
+};
+
+struct BandEnc {
+    double gain;
+    int bg, bs;
+    int root;                  // -1: no shape tree
+    int L;
 };
 
 // np.add.reduce of |a[i]| in NumPy's pairwise order (loops_utils.h.src pairwise_sum): blocks of at
@@ -341,120 +353,120 @@ __device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& 
     return acc;
 }
 
-// Phase A for one band on one warp.  x[0..L): band lines (shared); base/cap: the band's region in
-// the ping-pong workspaces wsA / wsB; words: the CTA's band bit buffers (zero-initialised), bit0:
-// first bit of this band's private buffer.  Returns the bits the band emits (0: all-zero band).
-__device__ __forceinline__ int warp_plan_gain_shape(const PvqTab& t, const double* x, int L, int R, double* wsA,
-                                                    double* wsB, int base, int cap, unsigned* words, int bit0, int band,
-                                                    ELeaf* leaves, int* nLeaves, int maxLeaves, int* err,
-                                                    FieldLog* lg = nullptr) {
+// One tree node on one warp (levels step).  count: pool fill; the node's children are appended.
+__device__ __forceinline__ void warp_plan_node(const PvqTab& t, TNode* nodes, int i, int* count, int maxNodes,
+                                               double* wsA, double* wsB, int* err) {
     const int lane = threadIdx.x & 31;
-    int bg, bs;
-    gs_alloc(t, R, L, &bg, &bs);
-    double ss = 0.0;
-    for (int i = lane; i < L; i += 32) ss += x[i] * x[i];
-    const double gain = sqrt(warp_sum(ss));
-    if (gain == 0.0) return 0;
-    int pos = bit0;                                     // lane-uniform write cursor
-    auto put = [&](unsigned long long v, int n) {       // fields written in phase A: theta, gain
-        if (lane == 0) {
-            BitW bw = {words, pos};
-            bw_put(bw, v, n);
-            log_field(lg, v, n);
-        }
-        pos += n;
-    };
-    if (bs != 0) {
-        for (int i = lane; i < L; i += 32) wsA[base + i] = x[i] / gain;
-        __syncwarp();
-        PvqNode st[24];
-        int sp = 0;
-        st[sp++] = {(short)base, (short)cap, (short)L, 0, bs};
-        while (sp > 0) {
-            const PvqNode nd = st[--sp];
-            double* cur = (nd.buf ? wsB : wsA) + nd.off;
-            double* oth = (nd.buf ? wsA : wsB) + nd.off;
-            if (nd.bits <= PVQ_SPLIT_BITS) {
-                long long K;
-                int w;
-                pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
-                if (K > 0) {
-                    int slot = 0, ls = -1;
-                    if (lane == 0) {
-                        slot = atomicAdd(nLeaves, 1);
-                        if (lg) { ls = *lg->count; log_field(lg, 0ull, w); }
-                        if (slot < maxLeaves) {
-                            ELeaf lf;
-                            lf.off = nd.off; lf.n = nd.n; lf.K = (int)K; lf.pos = pos;
-                            lf.buf = (unsigned char)nd.buf; lf.w = (unsigned char)w; lf.band = (unsigned char)band; lf.pad = 0;
-                            lf.logSlot = (short)ls; lf.pad2 = 0;
-                            leaves[slot] = lf;
-                        }
-                    }
-                    slot = __shfl_sync(0xffffffffu, slot, 0);
-                    if (slot >= maxLeaves) { *err |= PVQ_ERR_STACK; break; }
-                    pos += w;
-                } else {
-                    put(0ull, w);                      // empty leaf: index 0 in a 1-bit field
-                }
-                continue;
-            }
-            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
-            double sm = 0.0, sd = 0.0;
-            for (int i = lane; i < half; i += 32) {
-                double l = i < mid ? cur[i] : 0.0;       // odd n: the LEFT half is zero padded at its end
-                double r = cur[mid + i];
-                double M = (l + r) / 2.0, S = (l - r) / 2.0;
-                oth[i] = M;
-                oth[hc + i] = S;
-                sm += M * M;
-                sd += S * S;
-            }
-            const double nm = sqrt(warp_sum(sm)), ns = sqrt(warp_sum(sd));
-            __syncwarp();
-            for (int i = lane; i < half; i += 32) {
-                if (nm != 0.0) oth[i] = oth[i] / nm;
-                if (ns != 0.0) oth[hc + i] = oth[hc + i] / ns;
-            }
-            __syncwarp();
-            const double theta = nm == 0.0 ? 0.0 : atan(ns / nm);
-            int aT, aMs, aMid, aSide;
-            gs_alloc(t, nd.bits, half, &aT, &aMs);
-            const double hp = 1.5707963267948966;        // np.pi / 2
-            if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
-            const unsigned long long ti = quantize_uniform(theta / hp, aT);
-            const double tq = dequantize_uniform(ti, aT) * hp;
-            ms_alloc(aMs, tq, half, &aMid, &aSide);
-            put(ti, aT);
-            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
-            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide};
-            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid};
-        }
-        bg += bs - (pos - bit0);
+    const TNode nd = nodes[i];
+    if (nd.bits <= PVQ_SPLIT_BITS) {                      // leaf: pulses and index width from the table
+        long long K;
+        int w;
+        pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+        if (lane == 0) { nodes[i].K = (int)K; nodes[i].w = (unsigned char)w; }
+        return;
     }
-    const double g = log(1.0 + 255.0 * (gain / (double)L)) / log(256.0);      // mu_law_fn
-    if (bg < 0) bg = 0;
-    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
-    put(quantize_uniform(g, bg), bg);
+    double* cur = (nd.buf ? wsB : wsA) + nd.off;
+    double* oth = (nd.buf ? wsA : wsB) + nd.off;
+    const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = (1 << nd.capLog2) / 2;
+    double sm = 0.0, sd = 0.0;
+    for (int k = lane; k < half; k += 32) {
+        double l = k < mid ? cur[k] : 0.0;               // odd n: the LEFT half is zero padded at its end
+        double r = cur[mid + k];
+        double M = (l + r) / 2.0, S = (l - r) / 2.0;
+        oth[k] = M;
+        oth[hc + k] = S;
+        sm += M * M;
+        sd += S * S;
+    }
+    const double nm = sqrt(warp_sum(sm)), ns = sqrt(warp_sum(sd));
     __syncwarp();
-    return pos - bit0;
+    for (int k = lane; k < half; k += 32) {
+        if (nm != 0.0) oth[k] = oth[k] / nm;
+        if (ns != 0.0) oth[hc + k] = oth[hc + k] / ns;
+    }
+    const double theta = nm == 0.0 ? 0.0 : atan(ns / nm);
+    int aT, aMs, aMid, aSide;
+    gs_alloc(t, nd.bits, half, &aT, &aMs);
+    const double hp = 1.5707963267948966;                // np.pi / 2
+    if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+    const unsigned long long ti = quantize_uniform(theta / hp, aT);
+    const double tq = dequantize_uniform(ti, aT) * hp;
+    ms_alloc(aMs, tq, half, &aMid, &aSide);
+    if (lane == 0) {
+        const int nk = (aMid > 0) + (aSide > 0);
+        int slot = nk ? atomicAdd(count, nk) : 0;
+        short k0 = -1, k1 = -1;
+        if (slot + nk > maxNodes) {
+            *err |= PVQ_ERR_STACK;
+        } else {
+            TNode c;
+            c.val = 0ull; c.K = -2; c.n = (short)half; c.kid[0] = c.kid[1] = -1;
+            c.capLog2 = (unsigned char)(nd.capLog2 - 1); c.buf = (unsigned char)(1 - nd.buf); c.band = nd.band; c.w = 0;
+            c.logSlot = -1; c.pad = 0;
+            if (aMid > 0) { c.off = nd.off; c.bits = aMid; k0 = (short)slot; nodes[slot++] = c; }
+            if (aSide > 0) { c.off = (short)(nd.off + hc); c.bits = aSide; k1 = (short)slot; nodes[slot] = c; }
+        }
+        nodes[i].val = ti;
+        nodes[i].K = -1;
+        nodes[i].w = (unsigned char)aT;
+        nodes[i].kid[0] = k0;
+        nodes[i].kid[1] = k1;
+    }
 }
 
-// Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...  yws: int workspace
-// indexed like wsA / wsB.  logVal/logCap: the frame's field log ([band][logCap]) or nullptr.
-__device__ __forceinline__ void cta_quantize_leaves(const PvqTab& t, const ELeaf* leaves, int nLeaves, double* wsA,
+// Layout step for one band on ONE thread: stream order is pre-order [theta, mid.., side..], then
+// the gain, which also absorbs the unused shape bits.  words/bit0: the band's private bit buffer
+// (zero-initialised).  Returns the bits the band emits.
+__device__ __forceinline__ int thread_layout_band(TNode* nodes, const BandEnc& be, unsigned* words, int bit0, int* err,
+                                                  FieldLog* lg) {
+    int pos = bit0;
+    if (be.root >= 0) {
+        short st[48];
+        int sp = 0;
+        st[sp++] = (short)be.root;
+        while (sp > 0) {
+            const int i = st[--sp];
+            const int K = nodes[i].K, w = nodes[i].w;
+            if (K >= 0) {                                  // leaf; an empty one is index 0 in a 1-bit field
+                if (K > 0 && lg) nodes[i].logSlot = (short)*lg->count;
+                log_field(lg, 0ull, w);
+                nodes[i].bits = pos;
+            } else {
+                BitW bw = {words, pos};
+                bw_put(bw, nodes[i].val, w);
+                log_field(lg, nodes[i].val, w);
+                if (sp + 2 > 48) { *err |= PVQ_ERR_STACK; break; }
+                if (nodes[i].kid[1] >= 0) st[sp++] = nodes[i].kid[1];
+                if (nodes[i].kid[0] >= 0) st[sp++] = nodes[i].kid[0];
+            }
+            pos += w;
+        }
+    }
+    int bg = be.bg + (be.bs != 0 ? be.bs - (pos - bit0) : 0);
+    const double g = log(1.0 + 255.0 * (be.gain / (double)be.L)) / log(256.0);      // mu_law_fn
+    if (bg < 0) bg = 0;
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    const unsigned long long gi = quantize_uniform(g, bg);
+    BitW bw = {words, pos};
+    bw_put(bw, gi, bg);
+    log_field(lg, gi, bg);
+    return pos + bg - bit0;
+}
+
+// Leaves step: every thread of the CTA takes pool entries; leaf j -> warp j % nWarps, lane j / nWarps
+// (the serial per-leaf walks diverge, so they are spread over all warps and schedulers).
+__device__ __forceinline__ void cta_quantize_leaves(const PvqTab& t, const TNode* nodes, int nNodes, double* wsA,
                                                     double* wsB, int* yws, unsigned* words, unsigned long long* logVal,
                                                     int logCap, int tid, int nThreads, int* err) {
-    // leaf j goes to warp j % nWarps, lane j / nWarps: the serial per-leaf walks diverge, so spread
-    // them over all warps (and schedulers) instead of filling a few warps
     const int nWarps = nThreads >> 5;
-    for (int i = (tid & 31) * nWarps + (tid >> 5); i < nLeaves; i += nThreads) {
-        const ELeaf lf = leaves[i];
+    for (int i = (tid & 31) * nWarps + (tid >> 5); i < nNodes; i += nThreads) {
+        const TNode nd = nodes[i];
+        if (nd.K <= 0) continue;
         int werr = 0;
-        const unsigned long long idx = thread_quantize_pvq(t, (lf.buf ? wsB : wsA) + lf.off, (lf.buf ? wsA : wsB) + lf.off,
-                                                           yws + lf.off, lf.n, lf.K, &werr);
-        bw_put_at(words, lf.pos, idx, lf.w);
-        if (logVal && lf.logSlot >= 0 && lf.logSlot < logCap) logVal[(size_t)lf.band * logCap + lf.logSlot] = idx;
+        const unsigned long long idx = thread_quantize_pvq(t, (nd.buf ? wsB : wsA) + nd.off, (nd.buf ? wsA : wsB) + nd.off,
+                                                           yws + nd.off, nd.n, nd.K, &werr);
+        bw_put_at(words, nd.bits, idx, nd.w);
+        if (logVal && nd.logSlot >= 0 && nd.logSlot < logCap) logVal[(size_t)nd.band * logCap + nd.logSlot] = idx;
         if (werr) atomicOr(err, werr);
     }
 }
