@@ -140,3 +140,30 @@ def decode_host(ctx, h_pac, stream_off, h_pcm):
     if rc != 0 and rc != -4:
         _lib.check(rc)
     return np.array(po[:]), err.value
+
+
+# ---------------------------------------------------------------------- multi-GPU sharding
+def shard_streams(durations, world_size):
+    """Longest-processing-time-first assignment of independent streams to ranks:
+    returns a list of index lists, one per rank.  Streams share nothing (no bit reservoir,
+    coder/codec.py:288-299), so this is the whole of the N > 1 data path: no collective."""
+    order = sorted(range(len(durations)), key=lambda i: (-durations[i], i))
+    load = [0.0] * world_size
+    out = [[] for _ in range(world_size)]
+    for i in order:
+        r = min(range(world_size), key=lambda k: (load[k], k))
+        out[r].append(i)
+        load[r] += durations[i]
+    return [sorted(v) for v in out]
+
+
+def gather_manifest(local_rows, group=None):
+    """All-gather the per-stream (stream_id, n_bytes, error_flag) rows of every rank into one
+    table sorted by stream id: the only cross-rank exchange of a sharded run (a few bytes per
+    stream; works on any torch.distributed backend)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    rows = [None] * world
+    dist.all_gather_object(rows, [tuple(int(x) for x in r) for r in local_rows], group=group)
+    table = sorted(r for part in rows for r in part)
+    return table
