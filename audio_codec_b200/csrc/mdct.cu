@@ -2,7 +2,9 @@
 // Replaces coder/mdct.py:43-76 + coder/window.py for whole streams at once:
 // rows are (stream, channel) pairs, frames are hop-N/2 views into each row,
 // so no overlapped copy of the PCM is ever materialised.
+#include <algorithm>
 #include "mdct.cuh"
+#include "mdct_stream.cuh"
 #include "pac_api.h"
 
 // ---------------------------------------------------------------- forward
@@ -116,6 +118,58 @@ static int launch_inv(pac_ctx* ctx, const void* X, int nRows, int nFrames, int w
     return 0;
 }
 
+static bool aligned16(const void* p) { return ((size_t)p & 15) == 0; }
+
+// run length of a warp's walk: long enough to amortise the one halo block, short enough that
+// every warp of the grid gets several runs
+static int stream_seg(long long nRows, int nPerRow, int warps) {
+    long long total = nRows * (long long)nPerRow, want = total / ((long long)148 * warps * 4);
+    if (want < 1) want = 1;
+    if (want > 128) want = 128;
+    if (want > nPerRow) want = nPerRow;
+    return (int)want;
+}
+
+template <typename T>
+static int launch_fwd_stream(pac_ctx* ctx, const void* x, long long rowStride, int nRows, int nFrames, int window,
+                             void* coefs, cudaStream_t st) {
+    const PacTables<T>& t = tabs<T>(ctx);
+    constexpr int W = MsCfg<T>::WARPS;
+    const T* win = window == PAC_WIN_NONE ? nullptr : t.win_long + (size_t)window * 2048;
+    const int seg = stream_seg(nRows, nFrames, W), segs = (nFrames + seg - 1) / seg;
+    const long long units = (long long)nRows * segs;
+    const int grid = (int)std::min<long long>(148, (units + W - 1) / W);
+    const int vec = aligned16(x) && aligned16(coefs) && (rowStride * sizeof(T)) % 16 == 0;
+    auto kern = k_mdct_fwd_stream<T>;
+    const size_t smem = ms_smem_bytes<T>();
+    PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, W * 32, smem, st>>>((const T*)x, rowStride, nFrames, seg, segs, units, win,
+                                      reinterpret_cast<const cplx<T>*>(t.tw_mdct_long),
+                                      reinterpret_cast<const cplx<T>*>(t.tw_fft[2]), (T*)coefs, vec);
+    PAC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+template <typename T>
+static int launch_inv_stream(pac_ctx* ctx, const void* X, int nRows, int nFrames, int window, void* y,
+                             long long rowStride, cudaStream_t st) {
+    const PacTables<T>& t = tabs<T>(ctx);
+    constexpr int W = MsCfg<T>::WARPS;
+    const T* win = window == PAC_WIN_NONE ? nullptr : t.win_long + (size_t)window * 2048;
+    const int seg = stream_seg(nRows, nFrames + 1, W), segs = (nFrames + 1 + seg - 1) / seg;
+    const long long units = (long long)nRows * segs;
+    const int grid = (int)std::min<long long>(148, (units + W - 1) / W);
+    const int vec = aligned16(X) && aligned16(y) && (rowStride * sizeof(T)) % 16 == 0;
+    auto kern = k_imdct_ola_stream<T>;
+    const size_t smem = ms_smem_bytes<T>();
+    PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, W * 32, smem, st>>>((const T*)X, nFrames, seg, segs, units, win,
+                                      reinterpret_cast<const cplx<T>*>(t.tw_mdct_long),
+                                      reinterpret_cast<const cplx<T>*>(t.tw_fft[2]), (T*)y, rowStride, vec);
+    PAC_CHECK(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int pac_mdct_forward(pac_ctx* ctx, int dtype, const void* x, long long row_stride, int n_rows,
                                 int n_frames, int N, int window, void* coefs, void* stream) {
     if (!ctx) return PAC_ERR_ARG;
@@ -125,8 +179,8 @@ extern "C" int pac_mdct_forward(pac_ctx* ctx, int dtype, const void* x, long lon
     if (N == 256 && !(window == PAC_WIN_SINE || window == PAC_WIN_KAISER || window == PAC_WIN_NONE)) return PAC_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     PAC_CHECK(cudaSetDevice(ctx->device));
-    if (N == 2048 && dtype == PAC_F32) return launch_fwd<float, 2048>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
-    if (N == 2048 && dtype == PAC_F64) return launch_fwd<double, 2048>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
+    if (N == 2048 && dtype == PAC_F32) return launch_fwd_stream<float>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
+    if (N == 2048 && dtype == PAC_F64) return launch_fwd_stream<double>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
     if (N == 256 && dtype == PAC_F32) return launch_fwd<float, 256>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
     if (N == 256 && dtype == PAC_F64) return launch_fwd<double, 256>(ctx, x, row_stride, n_rows, n_frames, window, coefs, st);
     return PAC_ERR_ARG;
@@ -141,8 +195,8 @@ extern "C" int pac_imdct_ola(pac_ctx* ctx, int dtype, const void* coefs, int n_r
     if (N == 256 && !(window == PAC_WIN_SINE || window == PAC_WIN_KAISER || window == PAC_WIN_NONE)) return PAC_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     PAC_CHECK(cudaSetDevice(ctx->device));
-    if (N == 2048 && dtype == PAC_F32) return launch_inv<float, 2048>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
-    if (N == 2048 && dtype == PAC_F64) return launch_inv<double, 2048>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
+    if (N == 2048 && dtype == PAC_F32) return launch_inv_stream<float>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
+    if (N == 2048 && dtype == PAC_F64) return launch_inv_stream<double>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
     if (N == 256 && dtype == PAC_F32) return launch_inv<float, 256>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
     if (N == 256 && dtype == PAC_F64) return launch_inv<double, 256>(ctx, coefs, n_rows, n_frames, window, y, row_stride, st);
     return PAC_ERR_ARG;

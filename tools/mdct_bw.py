@@ -23,5 +23,6 @@ def run(F=1 << 20, dtype=torch.float32, window=_lib.W_SINE, iters=5):
     return dict(F=F, dtype=str(dtype), fwd_ms=tf, inv_ms=ti, fwd_gbs=algo / tf / 1e6, inv_gbs=algo / ti / 1e6, tdac_err=err)
 
 if __name__ == "__main__":
+    F = int(os.environ.get("MDCT_F", 1 << 20))
     for dt in (torch.float32, torch.float64):
-        print(json.dumps(run(1 << 20 if dt == torch.float32 else 1 << 19, dt)))
+        print(json.dumps(run(F if dt == torch.float32 else F // 2, dt, iters=int(os.environ.get("MDCT_ITERS", 5)))))
