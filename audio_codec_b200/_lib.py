@@ -20,7 +20,7 @@ PSY_SPL, PSY_INTENSITY, PSY_BARK, PSY_THRESH = range(4)
 class PacConfig(C.Structure):
     _fields_ = [("sample_rate", C.c_int), ("n_channels", C.c_int), ("n_mdct_lines", C.c_int),
                 ("n_scale_bits", C.c_int), ("n_mant_size_bits", C.c_int), ("use_sbr", C.c_int),
-                ("use_vq", C.c_int), ("target_bits_per_sample", C.c_double)]
+                ("use_vq", C.c_int), ("target_bits_per_sample", C.c_double), ("precision", C.c_int)]
 
 
 class PacError(RuntimeError):
@@ -53,7 +53,7 @@ def _load():
         # per-function ops
         "pac_window": (i, [vp, i, vp, ll, i, i, i, d, vp, vp]),
         "pac_transient_detect": (i, [vp, vp, ll, i, i, d, vp, vp]),
-        "pac_calc_smr": (i, [vp, vp, vp, vp, ll, i, i, pi, pi, vp, vp, vp]),
+        "pac_calc_smr": (i, [vp, i, vp, vp, vp, ll, i, i, pi, pi, vp, vp, vp]),
         "pac_psy_map": (i, [vp, i, vp, ll, vp, vp]),
         "pac_bit_alloc": (i, [vp, vp, i, i, pi, vp, ll, vp, vp]),
         "pac_quantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
@@ -107,7 +107,7 @@ class Context:
     (coder/pacfile.py:157-174, :699-707)."""
 
     def __init__(self, sample_rate=48000, n_channels=2, rate_kbps=128.0, use_vq=True, use_sbr=None,
-                 n_scale_bits=4, n_mant_size_bits=12, device=None, target_bits_per_sample=None):
+                 n_scale_bits=4, n_mant_size_bits=12, device=None, target_bits_per_sample=None, precision="f64"):
         import torch
         if not torch.cuda.is_available():
             raise PacError("no CUDA device: audio_codec_b200 has no CPU path")
@@ -117,7 +117,9 @@ class Context:
         if target_bits_per_sample is None:
             target_bits_per_sample = float(rate_kbps) / (sample_rate / 1000)     # coder/pacfile.py:702
         self.cfg = PacConfig(int(sample_rate), int(n_channels), 1024, int(n_scale_bits), int(n_mant_size_bits),
-                             int(bool(use_sbr)), int(bool(use_vq)), float(target_bits_per_sample))
+                             int(bool(use_sbr)), int(bool(use_vq)), float(target_bits_per_sample),
+                             {"f32": 0, "f64": 1}[precision])
+        self.precision = precision
         self.rate_kbps = rate_kbps
         h = C.c_void_p()
         check(lib.pac_create(self.device, C.byref(self.cfg), C.byref(h)))

@@ -45,7 +45,8 @@ struct DecArgs {
     int* err;
 };
 
-__global__ void __launch_bounds__(DEC_NT)
+template <typename T>
+__global__ void __launch_bounds__(DEC_NT, 3)
 k_decode(const PacDev* __restrict__ dev, DecArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DecSmem S;
@@ -68,10 +69,10 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a) {
     if (nBytes > 0) {
         if (!cur) {
             int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-            decode_frame<PAC_NLONG>(dev, S, recBits, shape, 0, a.err);
+            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err);
         } else {
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-                decode_frame<PAC_NSHORT>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err);
+                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err);
         }
     }
     double* dst = a.frames + (long long)cb * 2048;
@@ -196,9 +197,11 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
         a.buf = d_pac; a.payOff = (long long*)(sb + oPay); a.payBytes = (int*)(sb + oPayB);
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
         size_t smem = dec_smem_bytes();
-        PAC_CHECK(cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaEventRecord(ctx->ev[2], st);
-        k_decode<<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);
+        if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);
+        else k_decode<double><<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);
         cudaEventRecord(ctx->ev[3], st);
         ctx->evValid[1] = 1;
         PAC_CHECK(cudaGetLastError());

@@ -4,6 +4,7 @@
 // CTA-cooperative: every thread of a DEC_NT-thread CTA calls decode_frame.
 #pragma once
 #include "mdct.cuh"
+#include "psy.cuh"
 #include "pvq_dec.cuh"
 
 #define DEC_NT 256
@@ -49,7 +50,7 @@ __device__ __forceinline__ void dec_smem_carve(unsigned char* raw, DecSmem& S) {
 
 // Decode one frame of H = N/2 lines whose fields start at bit *bpos of the record;
 // adds its windowed IMDCT into y[yOff .. yOff+N).
-template <int N>
+template <int N, typename T>
 __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, long long recBits, int shape, int yOff,
                              int* err) {
     constexpr int H = N / 2, Q = N / 4;
@@ -185,18 +186,20 @@ __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, l
         __syncthreads();
     }
     // (4) undo the overall scale, IMDCT, synthesis window (coder/codec.py:85-89)
+    // T = float: the transform runs in fp32 (fast path; PCM within 1 LSB of the fp64 result).
+    const PacTables<T>& t = psy_tabs<T>(dev);
     const double inv = 1.0 / (double)(1 << scale);
-    const cplx<double>* tw = reinterpret_cast<const cplx<double>*>(isLong ? dev->d.tw_mdct_long : dev->d.tw_mdct_short);
-    const cplx<double>* roots = reinterpret_cast<const cplx<double>*>(dev->d.tw_fft[isLong ? 2 : 0]);
-    cplx<double>* fbuf = reinterpret_cast<cplx<double>*>(S.wsA);
-    double* v = S.wsA + 1024;
-    imdct_pre<double, N, 1, DEC_NT>(S.lines, inv, tw, fbuf, tid);
+    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(isLong ? t.tw_mdct_long : t.tw_mdct_short);
+    const cplx<T>* roots = reinterpret_cast<const cplx<T>*>(t.tw_fft[isLong ? 2 : 0]);
+    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(S.wsA);
+    T* v = reinterpret_cast<T*>(S.wsA + 1024);
+    imdct_pre<T, N, 1, DEC_NT, double>(S.lines, inv, tw, fbuf, tid);
     __syncthreads();
-    cta_fft<double, Q, 1, DEC_NT>(fbuf, roots, tid);
-    mdct_post<double, N, 1, DEC_NT>(fbuf, tw, 1.0, v, tid);
+    cta_fft<T, Q, 1, DEC_NT>(fbuf, roots, tid);
+    mdct_post<T, N, 1, DEC_NT>(fbuf, tw, (T)1, v, tid);
     __syncthreads();
-    const double* w = (isLong ? dev->d.win_long : dev->d.win_short) + shape * N;
-    for (int i = tid; i < N; i += DEC_NT) S.y[yOff + i] += w[i] * imdct_sample<double, N>(v, i);
+    const T* w = (isLong ? t.win_long : t.win_short) + shape * N;
+    for (int i = tid; i < N; i += DEC_NT) S.y[yOff + i] += (double)(w[i] * imdct_sample<T, N>(v, i));
     __syncthreads();
 }
 

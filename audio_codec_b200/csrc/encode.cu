@@ -98,6 +98,7 @@ struct EncArgs {
     int* err;              // [1] OR of soft error flags
 };
 
+template <typename T>
 __global__ void __launch_bounds__(ENC_NT, 3)
 k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -125,9 +126,10 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     const int dataBlk = j < nbs ? j : (j == nbs ? nbs - 1 : -1);
     const int priorBlk = j == 0 ? -1 : min(j - 1, nbs - 1);
     const short* base = a.pcm + ((long long)a.blkOff[s] * C + (long long)c * nbs) * 1024;
+    T* xs = reinterpret_cast<T*>(S.xs);
     for (int i = tid; i < 2048; i += ENC_NT) {
         int blk = i < 1024 ? priorBlk : dataBlk;
-        S.xs[i] = blk < 0 ? 0.0 : pcm_to_double(base[(long long)blk * 1024 + (i & 1023)]);
+        xs[i] = blk < 0 ? (T)0 : (T)pcm_to_double(base[(long long)blk * 1024 + (i & 1023)]);
     }
     for (int i = tid; i < REC_WORDS; i += ENC_NT) S.blockbuf[i] = 0u;
     if (tid == 0) {
@@ -146,16 +148,16 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     int declared = 4;                         // "+4 for block switching" (pacfile.py:560)
     if (!cur) {
         int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-        declared += encode_frame<PAC_NLONG>(dev, S, S.xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err);
+        declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err);
     } else {
         // zero sub-frame check (coder/pacfile.py:503-506): the block is dropped if ANY channel has one
         for (int sf = 0; sf < PAC_SUBFRAMES; ++sf) {
             bool nz = false;
-            for (int i = tid; i < PAC_NSHORT; i += ENC_NT) nz |= S.xs[448 + 128 * sf + i] != 0.0;
+            for (int i = tid; i < PAC_NSHORT; i += ENC_NT) nz |= xs[448 + 128 * sf + i] != (T)0;
             if (!__syncthreads_or(nz) && tid == 0) S.misc[4] = 1;
         }
         for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-            declared += encode_frame<PAC_NSHORT>(dev, S, S.xs + 448 + 128 * sf, PAC_WIN_SINE, true, last || nxt, false,
+            declared += encode_frame<PAC_NSHORT, T>(dev, S, xs + 448 + 128 * sf, PAC_WIN_SINE, true, last || nxt, false,
                                                  &S.misc[3], a.err);
     }
     __syncthreads();
@@ -335,9 +337,14 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
     size_t smem = enc_smem_bytes();
-    PAC_CHECK(cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaEventRecord(ctx->ev[0], st);
-    k_encode<<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
+    if (ctx->cfg.precision == PAC_F32) {
+        PAC_CHECK(cudaFuncSetAttribute(k_encode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_encode<float><<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
+    } else {
+        PAC_CHECK(cudaFuncSetAttribute(k_encode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_encode<double><<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
+    }
     cudaEventRecord(ctx->ev[1], st);
     ctx->evValid[0] = 1;
     PAC_CHECK(cudaGetLastError());

@@ -112,25 +112,29 @@ __device__ __forceinline__ double block_max(double v, double* red, int tid) {
 // Encode one frame of N samples at fx (shared) and append its fields to the block
 // bitstream at bit position *bpos.  Returns the DECLARED size in bits
 // (getNumBytesNeeded, coder/pacfile.py:342-361).  sbr: long frame of an SBR stream.
-template <int N>
-__device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const double* fx, int shape, bool cur,
+// T: arithmetic of the transform and psychoacoustic stages (double = parity path, float = fast
+// path); bit allocation and quantisation are always fp64 + integer.
+template <int N, typename T>
+__device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const T* fx, int shape, bool cur,
                             bool lastOrNext, bool sbr, int* bpos, int* err) {
     constexpr int H = N / 2, Q = N / 4;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
-    const PsyConst pc = psy_const<N>(dev);
-    const double* winTab = (N == PAC_NLONG) ? dev->d.win_long : dev->d.win_short;
-    const cplx<double>* tw = reinterpret_cast<const cplx<double>*>(N == PAC_NLONG ? dev->d.tw_mdct_long : dev->d.tw_mdct_short);
-    const cplx<double>* rootsQ = reinterpret_cast<const cplx<double>*>(dev->d.tw_fft[N == PAC_NLONG ? 2 : 0]);
-    cplx<double>* fbuf = reinterpret_cast<cplx<double>*>(S.fb);
+    const PsyConst<T> pc = psy_const<N, T>(dev);
+    const PacTables<T>& tabsT = psy_tabs<T>(dev);
+    const T* winTab = (N == PAC_NLONG) ? tabsT.win_long : tabsT.win_short;
+    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(N == PAC_NLONG ? tabsT.tw_mdct_long : tabsT.tw_mdct_short);
+    const cplx<T>* rootsQ = reinterpret_cast<const cplx<T>*>(tabsT.tw_fft[N == PAC_NLONG ? 2 : 0]);
+    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(S.fb);
+    T* mkT = reinterpret_cast<T*>(S.mk);
 
     PHASE_T0();
     // (1) window + MDCT (coder/codec.py:301-305)
-    mdct_fold<double, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
+    mdct_fold<T, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
     __syncthreads();
-    cta_fft<double, Q, 1, ENC_NT>(fbuf, rootsQ, tid);
-    mdct_post<double, N, 1, ENC_NT>(fbuf, tw, 2.0 / (double)N, S.lines, tid);
+    cta_fft<T, Q, 1, ENC_NT>(fbuf, rootsQ, tid);
+    mdct_post<T, N, 1, ENC_NT, double>(fbuf, tw, (T)2 / (T)N, S.lines, tid);
     __syncthreads();
     double mx = 0.0;
     for (int i = tid; i < H; i += ENC_NT) mx = fmax(mx, fabs(S.lines[i]));
@@ -138,17 +142,17 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
 
     PHASE(0);
     // (2) Hann FFT magnitude (shared by the psychoacoustic model and the SBR envelope)
-    hann_rfft_mag<N, ENC_NT>(fx, pc, fbuf, S.mk, tid);
+    hann_rfft_mag<N, ENC_NT, T>(fx, pc, fbuf, mkT, tid);
     if (sbr) {                                    // coder/codec.py:460-473
         double m2 = 0.0;
-        for (int k = tid; k <= H; k += ENC_NT) m2 = fmax(m2, S.mk[k]);
+        for (int k = tid; k <= H; k += ENC_NT) m2 = fmax(m2, (double)mkT[k]);
         double maxFFT = block_max(m2, S.red, tid) / (double)H;
         maxLine = fmax(maxLine, maxFFT);
         // per omitted band: sum of fftLines = |X|/H over the band (scale applied later, exact)
         for (int b = warp; b < nB; b += ENC_NT / 32) {
             if (!bands.omitted[b]) continue;
             double a = 0.0;
-            for (int i = lane; i < bands.nLines[b]; i += 32) a += S.mk[bands.lower[b] + i] / (double)H;
+            for (int i = lane; i < bands.nLines[b]; i += 32) a += (double)mkT[bands.lower[b] + i] / (double)H;
             a = warp_sum(a);
             if (lane == 0) S.env[b] = a;
         }
@@ -158,17 +162,17 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     const double up = (double)(1 << scale);
     for (int i = tid; i < H; i += ENC_NT) S.lines[i] *= up;
     for (int k = tid; k <= H; k += ENC_NT) {
-        double m = S.mk[k];
-        S.mk[k] = pc.norm * (m * m);
+        T m = mkT[k];
+        mkT[k] = pc.norm * (m * m);
     }
     __syncthreads();
 
     PHASE(1);
     // (3) psychoacoustic model -> SMR per band
-    const MaskerList ml = masker_list(S.fb);
-    const int nMask = pick_maskers<N, ENC_NT>(S.mk, pc, ml, tid);
-    masked_threshold<N, ENC_NT>(pc, ml, nMask, S.mk, tid);
-    band_smr<ENC_NT>(S.lines, scale, S.mk, bands, S.smr, tid);
+    const MaskerList<T> ml = masker_list<T>(reinterpret_cast<T*>(S.fb));
+    const int nMask = pick_maskers<N, ENC_NT, T>(mkT, pc, ml, tid);
+    masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mkT, tid);
+    band_smr<ENC_NT, T>(S.lines, scale, mkT, bands, S.smr, tid);
 
     PHASE(2);
     // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)

@@ -45,8 +45,8 @@ __device__ __forceinline__ void mdct_fold(const T* xs, int hop, const T* __restr
 }
 
 // Post-twiddle of the forward transform: fbuf [B][Q] -> X [B][M] (natural order), scaled.
-template <typename T, int N, int B, int NT>
-__device__ __forceinline__ void mdct_post(const cplx<T>* fbuf, const cplx<T>* __restrict__ tw, T scale, T* X,
+template <typename T, int N, int B, int NT, typename TO = T>
+__device__ __forceinline__ void mdct_post(const cplx<T>* fbuf, const cplx<T>* __restrict__ tw, T scale, TO* X,
                                           int tid) {
     constexpr int M = N / 2, Q = N / 4;
     for (int idx = tid; idx < B * Q; idx += NT) {
@@ -58,13 +58,13 @@ __device__ __forceinline__ void mdct_post(const cplx<T>* fbuf, const cplx<T>* __
 }
 
 // Pre-twiddle for the inverse (DCT-IV is its own inverse up to scale).
-template <typename T, int N, int B, int NT>
-__device__ __forceinline__ void imdct_pre(const T* X, T inScale, const cplx<T>* __restrict__ tw, cplx<T>* fbuf,
+template <typename T, int N, int B, int NT, typename TI = T>
+__device__ __forceinline__ void imdct_pre(const TI* X, TI inScale, const cplx<T>* __restrict__ tw, cplx<T>* fbuf,
                                           int tid) {
     constexpr int M = N / 2, Q = N / 4;
     for (int idx = tid; idx < B * Q; idx += NT) {
         int b = idx / Q, n = idx - b * Q;
-        cplx<T> t = {X[b * M + 2 * n] * inScale, X[b * M + M - 1 - 2 * n] * inScale};
+        cplx<T> t = {(T)(X[b * M + 2 * n] * inScale), (T)(X[b * M + M - 1 - 2 * n] * inScale)};
         fbuf[idx] = cmul(t, tw[n]);
     }
 }

@@ -101,35 +101,36 @@ extern "C" int pac_transient_detect(pac_ctx* ctx, const double* d_blocks, long l
 }
 
 // ---------------------------------------------------------------- psychoac.CalcSMRs / getMaskedThreshold
-template <int N>
+template <int N, typename T>
 __global__ void __launch_bounds__(ENC_NT)
 k_calc_smr(const PacDev* __restrict__ dev, const double* __restrict__ data, const double* __restrict__ mdct,
            const int* __restrict__ scale, PacBands bands, double* __restrict__ smr, double* __restrict__ maskOut) {
     constexpr int H = N / 2;
+    constexpr int FB = N * (int)sizeof(T) > PSY_LIST_BYTES ? N * (int)sizeof(T) : PSY_LIST_BYTES;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* xs = reinterpret_cast<double*>(smem_raw);     // [N]
-    double* fb = xs + N;                                  // [N]  FFT buffer, then masker list (3 x 640 max)
-    double* mk = fb + (N > 1920 ? N : 1920);              // [H + 16]
-    double* lines = mk + H + 16;                          // [H]
+    double* lines = reinterpret_cast<double*>(smem_raw);  // [H]
     double* smrS = lines + H;                             // [32]
+    T* fb = reinterpret_cast<T*>(smrS + 32);              // FB bytes: FFT buffer, then the masker list
+    T* xs = reinterpret_cast<T*>(smem_raw + sizeof(double) * (H + 32) + FB);   // [N]
+    T* mk = xs + N;                                       // [H + 16]
     const int tid = threadIdx.x;
     const long long f = blockIdx.x;
-    const PsyConst pc = psy_const<N>(dev);
-    for (int i = tid; i < N; i += ENC_NT) xs[i] = data[f * N + i];
+    const PsyConst<T> pc = psy_const<N, T>(dev);
+    for (int i = tid; i < N; i += ENC_NT) xs[i] = (T)data[f * N + i];
     if (mdct) for (int i = tid; i < H; i += ENC_NT) lines[i] = mdct[f * H + i];
     __syncthreads();
-    hann_rfft_mag<N, ENC_NT>(xs, pc, reinterpret_cast<cplx<double>*>(fb), mk, tid);
+    hann_rfft_mag<N, ENC_NT, T>(xs, pc, reinterpret_cast<cplx<T>*>(fb), mk, tid);
     for (int k = tid; k <= H; k += ENC_NT) {
-        double m = mk[k];
+        T m = mk[k];
         mk[k] = pc.norm * (m * m);
     }
     __syncthreads();
-    const MaskerList ml = masker_list(fb);
-    const int nMask = pick_maskers<N, ENC_NT>(mk, pc, ml, tid);
-    masked_threshold<N, ENC_NT>(pc, ml, nMask, mk, tid);
-    if (maskOut) for (int i = tid; i < H; i += ENC_NT) maskOut[f * H + i] = mk[i];
+    const MaskerList<T> ml = masker_list<T>(fb);
+    const int nMask = pick_maskers<N, ENC_NT, T>(mk, pc, ml, tid);
+    masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mk, tid);
+    if (maskOut) for (int i = tid; i < H; i += ENC_NT) maskOut[f * H + i] = (double)mk[i];
     if (smr) {
-        band_smr<ENC_NT>(lines, scale[f], mk, bands, smrS, tid);
+        band_smr<ENC_NT, T>(lines, scale[f], mk, bands, smrS, tid);
         if (tid < bands.nBands) smr[f * bands.nBands + tid] = smrS[tid];
     }
 }
@@ -146,7 +147,7 @@ static int fill_bands(PacBands* b, int n_bands, const int* h_lower, const int* h
     return 0;
 }
 
-extern "C" int pac_calc_smr(pac_ctx* ctx, const double* d_data, const double* d_mdct, const int* d_scale,
+extern "C" int pac_calc_smr(pac_ctx* ctx, int dtype, const double* d_data, const double* d_mdct, const int* d_scale,
                             long long n_frames, int N, int n_bands, const int* h_lower, const int* h_nlines,
                             double* d_smr, double* d_mask, void* stream) {
     if (!ctx || (N != PAC_NLONG && N != PAC_NSHORT)) return PAC_ERR_ARG;
@@ -162,14 +163,19 @@ extern "C" int pac_calc_smr(pac_ctx* ctx, const double* d_data, const double* d_
     PAC_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
     const int H = N / 2;
-    size_t smem = sizeof(double) * ((size_t)N + (N > 1920 ? N : 1920) + H + 16 + H + 32);
-    if (N == PAC_NLONG) {
-        PAC_CHECK(cudaFuncSetAttribute(k_calc_smr<PAC_NLONG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_calc_smr<PAC_NLONG><<<(unsigned)n_frames, ENC_NT, smem, st>>>(ctx->dev, d_data, d_mdct, d_scale, b, d_smr, d_mask);
-    } else {
-        PAC_CHECK(cudaFuncSetAttribute(k_calc_smr<PAC_NSHORT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_calc_smr<PAC_NSHORT><<<(unsigned)n_frames, ENC_NT, smem, st>>>(ctx->dev, d_data, d_mdct, d_scale, b, d_smr, d_mask);
-    }
+    if (dtype != PAC_F32 && dtype != PAC_F64) return PAC_ERR_ARG;
+    const size_t eb = dtype == PAC_F32 ? sizeof(float) : sizeof(double);
+    const size_t fbB = (size_t)N * eb > PSY_LIST_BYTES ? (size_t)N * eb : PSY_LIST_BYTES;
+    const size_t smem = sizeof(double) * (H + 32) + fbB + eb * ((size_t)N + H + 16);
+    auto go = [&](auto kern) -> int {
+        PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)n_frames, ENC_NT, smem, st>>>(ctx->dev, d_data, d_mdct, d_scale, b, d_smr, d_mask);
+        return 0;
+    };
+    int rc2;
+    if (dtype == PAC_F32) rc2 = N == PAC_NLONG ? go(k_calc_smr<PAC_NLONG, float>) : go(k_calc_smr<PAC_NSHORT, float>);
+    else rc2 = N == PAC_NLONG ? go(k_calc_smr<PAC_NLONG, double>) : go(k_calc_smr<PAC_NSHORT, double>);
+    if (rc2) return rc2;
     OPS_LAUNCH_CHECK();
     return 0;
 }
@@ -551,6 +557,7 @@ struct FrameEncArgs {
     int* err;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(ENC_NT)
 k_encode_frames(const PacDev* __restrict__ dev, FrameEncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -560,7 +567,8 @@ k_encode_frames(const PacDev* __restrict__ dev, FrameEncArgs a) {
     const long long f = blockIdx.x;
     const bool last = a.flags[f] & 1, cur = (a.flags[f] >> 1) & 1, nxt = (a.flags[f] >> 2) & 1;
     const int nIn = a.mode == 0 ? 2048 : a.N;
-    for (int i = tid; i < 2048; i += ENC_NT) S.xs[i] = i < nIn ? a.x[f * nIn + i] : 0.0;
+    T* xs = reinterpret_cast<T*>(S.xs);
+    for (int i = tid; i < 2048; i += ENC_NT) xs[i] = i < nIn ? (T)a.x[f * nIn + i] : (T)0;
     for (int i = tid; i < REC_WORDS; i += ENC_NT) S.blockbuf[i] = 0u;
     if (a.mode == 1 && a.logVal) {
         S.logVal = a.logVal + (size_t)f * 32 * a.logCap;
@@ -589,23 +597,23 @@ k_encode_frames(const PacDev* __restrict__ dev, FrameEncArgs a) {
         declared = 4;
         if (!cur) {
             int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-            declared += encode_frame<PAC_NLONG>(dev, S, S.xs, shape, false, last || nxt, a.sbr != 0, &S.misc[3], a.err);
+            declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, a.sbr != 0, &S.misc[3], a.err);
         } else {
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf) {
                 bool nz = false;
-                for (int i = tid; i < PAC_NSHORT; i += ENC_NT) nz |= S.xs[448 + 128 * sf + i] != 0.0;
+                for (int i = tid; i < PAC_NSHORT; i += ENC_NT) nz |= xs[448 + 128 * sf + i] != (T)0;
                 if (!__syncthreads_or(nz) && tid == 0) S.misc[4] = 1;
             }
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-                declared += encode_frame<PAC_NSHORT>(dev, S, S.xs + 448 + 128 * sf, PAC_WIN_SINE, true, last || nxt,
+                declared += encode_frame<PAC_NSHORT, T>(dev, S, xs + 448 + 128 * sf, PAC_WIN_SINE, true, last || nxt,
                                                      false, &S.misc[3], a.err);
         }
     } else if (a.N == PAC_NLONG) {
         // codec.getCorrectWindow (coder/codec.py:30-44); cur on a 2048 frame still selects the sine window
         int shape = cur ? PAC_WIN_SINE : (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-        declared = encode_frame<PAC_NLONG>(dev, S, S.xs, shape, cur, last || nxt, a.sbr != 0, &S.misc[3], a.err);
+        declared = encode_frame<PAC_NLONG, T>(dev, S, xs, shape, cur, last || nxt, a.sbr != 0, &S.misc[3], a.err);
     } else {
-        declared = encode_frame<PAC_NSHORT>(dev, S, S.xs, PAC_WIN_SINE, cur, last || nxt, false, &S.misc[3], a.err);
+        declared = encode_frame<PAC_NSHORT, T>(dev, S, xs, PAC_WIN_SINE, cur, last || nxt, false, &S.misc[3], a.err);
     }
     __syncthreads();
     const int nBytes = (declared + 7) / 8;
@@ -635,8 +643,13 @@ static int run_encode_frames(pac_ctx* ctx, FrameEncArgs& a, long long n, int* h_
     PAC_CHECK(cudaMemsetAsync(scr, 0, sizeof(int), st));
     a.err = (int*)scr;
     const size_t smem = enc_smem_bytes();
-    PAC_CHECK(cudaFuncSetAttribute(k_encode_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_encode_frames<<<(unsigned)n, ENC_NT, smem, st>>>(ctx->dev, a);
+    if (ctx->cfg.precision == PAC_F32) {
+        PAC_CHECK(cudaFuncSetAttribute(k_encode_frames<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_encode_frames<float><<<(unsigned)n, ENC_NT, smem, st>>>(ctx->dev, a);
+    } else {
+        PAC_CHECK(cudaFuncSetAttribute(k_encode_frames<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_encode_frames<double><<<(unsigned)n, ENC_NT, smem, st>>>(ctx->dev, a);
+    }
     OPS_LAUNCH_CHECK();
     int err = 0;
     PAC_CHECK(cudaMemcpyAsync(&err, scr, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -695,6 +708,7 @@ struct FrameDecArgs {
     int* err;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(DEC_NT)
 k_decode_frames(const PacDev* __restrict__ dev, FrameDecArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -720,10 +734,10 @@ k_decode_frames(const PacDev* __restrict__ dev, FrameDecArgs a) {
         if (nBytes > 0) {
             if (!cur) {
                 int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-                decode_frame<PAC_NLONG>(dev, S, recBits, shape, 0, a.err);
+                decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err);
             } else {
                 for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-                    decode_frame<PAC_NSHORT>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err);
+                    decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err);
             }
         }
     } else {
@@ -733,9 +747,9 @@ k_decode_frames(const PacDev* __restrict__ dev, FrameDecArgs a) {
         nOut = a.N;
         if (a.N == PAC_NLONG) {
             int shape = cur ? PAC_WIN_SINE : (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-            decode_frame<PAC_NLONG>(dev, S, recBits, shape, 0, a.err);
+            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err);
         } else {
-            decode_frame<PAC_NSHORT>(dev, S, recBits, PAC_WIN_SINE, 0, a.err);
+            decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 0, a.err);
         }
     }
     __syncthreads();
@@ -751,8 +765,10 @@ static int run_decode_frames(pac_ctx* ctx, FrameDecArgs& a, long long n, int* h_
     PAC_CHECK(cudaMemsetAsync(scr, 0, sizeof(int), st));
     a.err = (int*)scr;
     size_t smem = dec_smem_bytes();
-    PAC_CHECK(cudaFuncSetAttribute(k_decode_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_decode_frames<<<(unsigned)n, DEC_NT, smem, st>>>(ctx->dev, a);
+    PAC_CHECK(cudaFuncSetAttribute(k_decode_frames<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PAC_CHECK(cudaFuncSetAttribute(k_decode_frames<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (ctx->cfg.precision == PAC_F32) k_decode_frames<float><<<(unsigned)n, DEC_NT, smem, st>>>(ctx->dev, a);
+    else k_decode_frames<double><<<(unsigned)n, DEC_NT, smem, st>>>(ctx->dev, a);
     OPS_LAUNCH_CHECK();
     int err = 0;
     PAC_CHECK(cudaMemcpyAsync(&err, scr, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -337,6 +337,7 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     if (cudaSetDevice(device) != cudaSuccess) return PAC_ERR_ARG;
     pac_ctx* c = new pac_ctx();
     c->device = device;
+    if (cfg->precision != PAC_F32 && cfg->precision != PAC_F64) return PAC_ERR_ARG;
     c->cfg = *cfg;
     c->dev = nullptr;
     c->scratch = nullptr;

@@ -72,10 +72,10 @@ def parse_header(buf):
                 n_mant_size_bits=nmsb, use_sbr=bool(sbr), use_vq=bool(vq), n_lines=lines)
 
 
-def context_for_header(h):
+def context_for_header(h, precision="f64"):
     ctx = _lib.default_context(h["sample_rate"], n_channels=h["n_channels"], use_vq=h["use_vq"],
                                use_sbr=h["use_sbr"], n_scale_bits=h["n_scale_bits"],
-                               n_mant_size_bits=h["n_mant_size_bits"])
+                               n_mant_size_bits=h["n_mant_size_bits"], precision=precision)
     nl, _ = ctx.bands()
     if tuple(int(v) for v in nl) != tuple(h["n_lines"]) or h["n_mdct_lines"] != 1024:
         raise _lib.PacError("unsupported band layout in .pac header")
@@ -99,10 +99,32 @@ def decode_device(ctx, d_pac, stream_off, d_pcm=None):
     return d_pcm, np.array(po[:]), err.value
 
 
-def decode_streams(pac_list):
+def block_records(buf):
+    """Split one .pac stream into its per-(block, channel) records (the bytes after each <L
+    length prefix, coder/pacfile.py:239-256).  Host helper for comparing two encodings."""
+    import struct
+    h = parse_header(buf)
+    pos = 30 + 2 * len(h["n_lines"])
+    out = []
+    while pos + 4 <= len(buf):
+        n = struct.unpack_from("<L", buf, pos)[0]
+        out.append(bytes(buf[pos + 4:pos + 4 + n]))
+        pos += 4 + n
+    return out
+
+
+def record_mismatch_rate(a, b):
+    """Fraction of (block, channel) records that differ between two encodings of the same PCM."""
+    ra, rb = block_records(a), block_records(b)
+    n = max(len(ra), len(rb))
+    same = sum(1 for x, y in zip(ra, rb) if x == y)
+    return (n - same) / max(n, 1)
+
+
+def decode_streams(pac_list, precision="f64"):
     """Host convenience: list of .pac bytes (same configuration) -> list of int16 [C, n]."""
     h = parse_header(pac_list[0])
-    ctx = context_for_header(h)
+    ctx = context_for_header(h, precision)
     off = np.concatenate([[0], np.cumsum([len(b) for b in pac_list])])
     d_pac = torch.from_numpy(np.frombuffer(b"".join(pac_list), dtype=np.uint8).copy()).cuda()
     d_pcm, po, err = decode_device(ctx, d_pac, off)

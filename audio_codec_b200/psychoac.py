@@ -123,7 +123,7 @@ def getMaskedThreshold(data, MDCTdata, MDCTscale, sampleRate, sfBands):
     d, d2, _, _, n, N, was_np = _frames(data, None, None)
     ctx = _lib.default_context(int(sampleRate))
     mask = torch.empty((n, N // 2), dtype=torch.float64, device=d.device)
-    _lib.check(_lib.lib.pac_calc_smr(ctx.h, ptr(d2), None, None, n, N, 0, None, None, None, ptr(mask),
+    _lib.check(_lib.lib.pac_calc_smr(ctx.h, ctx.cfg.precision, ptr(d2), None, None, n, N, 0, None, None, None, ptr(mask),
                                      _lib.stream_ptr()))
     return from_device(mask.reshape(*d.shape[:-1], N // 2), was_np)
 
@@ -136,6 +136,6 @@ def CalcSMRs(data, MDCTdata, MDCTscale, sampleRate, sfBands):
     lo, lo_p = _int_array(sfBands.lowerLine)
     nl, nl_p = _int_array(sfBands.nLines)
     smr = torch.empty((n, sfBands.nBands), dtype=torch.float64, device=d.device)
-    _lib.check(_lib.lib.pac_calc_smr(ctx.h, ptr(d2), ptr(m), ptr(s), n, N, int(sfBands.nBands), lo_p, nl_p, ptr(smr),
+    _lib.check(_lib.lib.pac_calc_smr(ctx.h, ctx.cfg.precision, ptr(d2), ptr(m), ptr(s), n, N, int(sfBands.nBands), lo_p, nl_p, ptr(smr),
                                      None, _lib.stream_ptr()))
     return from_device(smr.reshape(*d.shape[:-1], sfBands.nBands), was_np)

@@ -146,6 +146,80 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def mdct_leg(ctx, peak):
+    """BASELINE config 2 / the metric's "MDCT HBM GB/s": batched window+MDCT and IMDCT+window+OLA,
+    N = 2048, sine window, 1 Mi synthetic stereo frames (fp32), timed with CUDA events; algorithmic
+    bytes = one read + one write of 1024 values per channel-frame and direction."""
+    import torch
+    from audio_codec_b200 import _lib, mdct
+    F = int(os.environ.get("PAC_MDCT_FRAMES", 1 << 20))
+    out = {"workload": f"{F} stereo frames, N=2048, sine window, inputs {2 * (F + 1) * 4096 / 1e9:.1f} GB (larger than L2)"}
+    for name, dt, f in (("f32", torch.float32, F), ("f64", torch.float64, F // 2)):
+        g = torch.Generator(device="cuda").manual_seed(422)
+        x = (0.25 * torch.randn((2, (f + 1) * 1024), generator=g, device="cuda", dtype=torch.float32)).clamp_(-1, 1).to(dt)
+        X = mdct.mdct_frames(x, 2048, _lib.W_SINE, ctx)
+        y = mdct.imdct_ola(X, 2048, _lib.W_SINE, ctx)
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        tf = ti = 0.0
+        it = 5
+        for _ in range(it):
+            ev[0].record()
+            X = mdct.mdct_frames(x, 2048, _lib.W_SINE, ctx)
+            ev[1].record()
+            y = mdct.imdct_ola(X, 2048, _lib.W_SINE, ctx)
+            ev[2].record()
+            torch.cuda.synchronize()
+            tf += ev[0].elapsed_time(ev[1]) / it
+            ti += ev[1].elapsed_time(ev[2]) / it
+        algo = 2 * f * 1024 * x.element_size() * 2
+        err = float((y[:, 1024:-1024] - x[:, 1024:-1024]).abs().max())
+        out[name] = {"fwd_ms": tf, "inv_ms": ti, "fwd_gbs": algo / tf / 1e6, "inv_gbs": algo / ti / 1e6,
+                     "fwd_frac": algo / tf / 1e6 / peak, "inv_frac": algo / ti / 1e6 / peak, "tdac_max_err": err}
+        del x, X, y
+    return out
+
+
+def fp32_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out64, off64, audio_s, steps):
+    """The fp32 fast path (precision="f32": transforms + psychoacoustic model in fp32) on the same
+    workload, device resident, plus its code-mismatch rate against the fp64 encoding just made
+    (fraction of (block, channel) records whose bytes differ, first 8 streams)."""
+    import torch
+    ctx = _lib.Context(sample_rate=FS, n_channels=2, rate_kbps=RATE, device=local, precision="f32")
+    d_out = torch.empty_like(d_out64)
+    d_dec = None
+    for _ in range(2):
+        _, off, err = engine.encode_device(ctx, d_pcm, nbs, hdr, d_out)
+        d_dec, po, err2 = engine.decode_device(ctx, d_out, off, d_dec)
+    assert (err | err2) == 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    enc_ms, dec_ms = [], []
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        _, off, _ = engine.encode_device(ctx, d_pcm, nbs, hdr, d_out)
+        engine.decode_device(ctx, d_out, off, d_dec)
+        a, b = ctx.last_kernel_ms()
+        enc_ms.append(a)
+        dec_ms.append(b)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    k = min(8, len(nbs))
+    a = d_out[:int(off[k])].cpu().numpy().tobytes()
+    b = d_out64[:int(off64[k])].cpu().numpy().tobytes()
+    diff = tot = 0
+    for s in range(k):
+        ra = engine.block_records(a[int(off[s]):int(off[s + 1])])
+        rb = engine.block_records(b[int(off64[s]):int(off64[s + 1])])
+        tot += max(len(ra), len(rb))
+        diff += max(len(ra), len(rb)) - sum(1 for x, y in zip(ra, rb) if x == y)
+    return {"value": audio_s * steps / (ms * 1e-3), "unit": "audio-s/s (this rank)", "k_encode_ms": float(np.mean(enc_ms)),
+            "k_decode_ms": float(np.mean(dec_ms)), "record_mismatch_rate": diff / max(tot, 1),
+            "mismatch_sample": f"{tot} (block, channel) records of the first {k} streams vs the fp64 encoding",
+            "tolerance": "MDCT/SMR 1e-5 rel, PCM <= 1 LSB (tests/test_fp32_gpu.py)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -153,6 +227,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-mdct", action="store_true", help="skip the MDCT/IMDCT bandwidth leg (BASELINE config 2)")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the fp32 fast-path leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -258,13 +334,25 @@ def main():
                            "parallelism": f"streams sharded over {world} GPU(s), no collective on the data path"},
                 "e2e": {"value": world * audio_s * args.steps / (host_ms_scaled * 1e-3), "unit": "audio-s/s",
                         "h2d_bytes_per_step": d_pcm.numel() * 2 + pac_bytes, "d2h_bytes_per_step": pac_bytes + int(po[-1]) * 2},
-                "gpu_launches": 9 * args.steps,
+                # per step: k_transient, k_encode, k_sizes, 2 x cub scan, k_gather, k_headers; 2 x k_walk, k_decode, k_ola
+                "gpu_launches": 11 * args.steps,
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "kernel": "k_encode", "achieved": ach, "peak": peak, "unit": "GB/s",
                              "frac": ach / peak, "traffic": None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                              "k_encode_ms": ke_ms, "k_decode_ms": float(np.mean(dec_ms)),
                              "note": "encode is compute/latency bound (fp64 psychoacoustics + PVQ), see DESIGN.md"}}
+        try:        # dram bytes per k_encode launch from the committed ncu capture of this same configuration
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if tr.get("streams") == S and tr.get("seconds") == SECONDS:
+                line["roofline"]["traffic"] = tr["k_encode_dram_bytes"]
+                line["roofline"]["traffic_k_decode"] = tr.get("k_decode_dram_bytes")
+        except Exception:
+            pass
+        if not args.no_mdct:
+            line["mdct"] = mdct_leg(ctx, peak)
+        if not args.no_fp32:
+            line["fp32"] = fp32_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out, off, audio_s, args.steps)
         if not args.no_cpu:
             cs = float(os.environ.get("PAC_CPU_SECONDS", 12.0))
             sample = pcm[0, :, :int(cs * FS)].cpu().numpy()

@@ -45,6 +45,9 @@ typedef struct pac_config {
     int use_sbr;                /* coder/pacfile.py:704 */
     int use_vq;                 /* coder/pacfile.py:705 */
     double target_bits_per_sample; /* rate_kbps / (fs/1000), per channel (pacfile.py:702) */
+    int precision;              /* PAC_F64: the reference's fp64 arithmetic, bit-exact .pac / PCM (default);
+                                 * PAC_F32: fast path - transforms and psychoacoustic model in fp32 (MDCT and
+                                 * SMRs within 1e-5, decoded PCM within 1 LSB); quantisers stay fp64 + integer */
 } pac_config;
 
 int pac_create(int device, const pac_config* cfg, pac_ctx** out);
@@ -141,8 +144,10 @@ int pac_transient_detect(pac_ctx* ctx, const double* d_blocks, long long n_block
 /* psychoac.CalcSMRs / getMaskedThreshold (coder/psychoac.py:163-291) for n_frames frames of
  * N (2048 | 256) samples at the context's sample rate.  d_mdct: MDCT lines scaled by 2^d_scale[f].
  * Bands as ScaleFactorBands gives them (lowerLine, nLines).  d_smr [n][n_bands] and/or
- * d_mask [n][N/2] (masked threshold in dB SPL at the MDCT lines); either may be NULL. */
-int pac_calc_smr(pac_ctx* ctx, const double* d_data, const double* d_mdct, const int* d_scale, long long n_frames,
+ * d_mask [n][N/2] (masked threshold in dB SPL at the MDCT lines); either may be NULL.
+ * dtype: arithmetic of the model (PAC_F64 = the reference's; PAC_F32 = fast path, SMRs within
+ * 1e-5 of their range); the buffers are fp64 either way. */
+int pac_calc_smr(pac_ctx* ctx, int dtype, const double* d_data, const double* d_mdct, const int* d_scale, long long n_frames,
                  int N, int n_bands, const int* h_lower, const int* h_nlines, double* d_smr, double* d_mask,
                  void* stream);
 
