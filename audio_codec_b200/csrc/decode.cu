@@ -196,7 +196,7 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
         DecArgs a;
         a.buf = d_pac; a.payOff = (long long*)(sb + oPay); a.payBytes = (int*)(sb + oPayB);
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
-        size_t smem = dec_smem_bytes();
+        size_t smem = dec_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
         PAC_CHECK(cudaFuncSetAttribute(k_decode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PAC_CHECK(cudaFuncSetAttribute(k_decode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaEventRecord(ctx->ev[2], st);

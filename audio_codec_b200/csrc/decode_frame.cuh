@@ -24,6 +24,7 @@ struct DecSmem {
     int* misc;            // [16]; [7] = number of tree nodes of the current frame
     DNode* nodes;         // [DEC_MAX_NODES] split-tree nodes of the current frame (phase A -> B -> C)
     BandDec* bd;          // [32]
+    unsigned char* raw;   // base of the carve
 };
 
 __host__ __device__ constexpr size_t dec_smem_bytes() {
@@ -33,6 +34,7 @@ __host__ __device__ constexpr size_t dec_smem_bytes() {
 
 __device__ __forceinline__ void dec_smem_carve(unsigned char* raw, DecSmem& S) {
     double* dp = reinterpret_cast<double*>(raw);
+    S.raw = raw;
     S.lines = dp; dp += 1024;
     S.wsA = dp; dp += 2048;
     S.wsB = dp; dp += 2048;
@@ -48,14 +50,20 @@ __device__ __forceinline__ void dec_smem_carve(unsigned char* raw, DecSmem& S) {
     S.rec = reinterpret_cast<unsigned char*>(ip);
 }
 
-// Decode one frame of H = N/2 lines whose fields start at bit *bpos of the record;
-// adds its windowed IMDCT into y[yOff .. yOff+N).
-template <int N, typename T>
-__device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, long long recBits, int shape, int yOff,
-                             int* err) {
-    constexpr int H = N / 2, Q = N / 4;
+// Steps (1)-(3) of a frame: header parse, dequantisation of every band, SBR reconstruction ->
+// S.lines (still scaled).  One out-of-line copy shared by the long / short frames of both
+// precisions (the kernel is instruction-cache bound otherwise).  Returns the overall scale.
+#ifdef PAC_FRONT_INLINE
+__device__ __forceinline__
+#else
+static __device__ __noinline__
+#endif
+int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long recBits,
+                                                bool isLong, int* err) {
+    DecSmem S;
+    dec_smem_carve(raw, S);
+    const int H = isLong ? PAC_HALF_LONG : PAC_HALF_SHORT;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const bool isLong = N == PAC_NLONG;
     const PacBands& bands = isLong ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
     // (1) frame header: overall scale, bit allocations (+ BFP scale factors): thread 0
@@ -185,6 +193,18 @@ __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, l
         }
         __syncthreads();
     }
+    return scale;
+}
+
+// Decode one frame of H = N/2 lines whose fields start at bit S.misc[3] of the record;
+// adds its windowed IMDCT into y[yOff .. yOff+N).
+template <int N, typename T>
+__device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, long long recBits, int shape, int yOff,
+                             int* err) {
+    constexpr int Q = N / 4;
+    const int tid = threadIdx.x;
+    const bool isLong = N == PAC_NLONG;
+    const int scale = decode_front(dev, S.raw, recBits, isLong, err);
     // (4) undo the overall scale, IMDCT, synthesis window (coder/codec.py:85-89)
     // T = float: the transform runs in fp32 (fast path; PCM within 1 LSB of the fp64 result).
     const PacTables<T>& t = psy_tabs<T>(dev);

@@ -336,7 +336,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     EncArgs a;
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
-    size_t smem = enc_smem_bytes();
+    size_t smem = enc_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
     cudaEventRecord(ctx->ev[0], st);
     if (ctx->cfg.precision == PAC_F32) {
         PAC_CHECK(cudaFuncSetAttribute(k_encode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -60,7 +60,9 @@ struct EncSmem {
     int logCap;
     TNode* nodes;      // [ENC_MAX_NODES] split-tree nodes of the current frame
     BandEnc* bandEnc;  // [32]
+    unsigned char* raw;  // base of the carve (encode_back re-derives the pointers from it)
 };
+struct EncLog { unsigned long long* val; int* w; int* cnt; int cap; };
 
 __host__ __device__ constexpr size_t enc_smem_bytes() {
     return (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) +
@@ -70,6 +72,7 @@ __host__ __device__ constexpr size_t enc_smem_bytes() {
 
 __device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
     double* dp = reinterpret_cast<double*>(raw);
+    S.raw = raw;
     S.xs = dp; dp += 2048;
     S.fb = dp; dp += 2048;
     S.lines = dp; dp += 1024;
@@ -109,72 +112,21 @@ __device__ __forceinline__ double block_max(double v, double* red, int tid) {
     return r;
 }
 
-// Encode one frame of N samples at fx (shared) and append its fields to the block
-// bitstream at bit position *bpos.  Returns the DECLARED size in bits
-// (getNumBytesNeeded, coder/pacfile.py:342-361).  sbr: long frame of an SBR stream.
-// T: arithmetic of the transform and psychoacoustic stages (double = parity path, float = fast
-// path); bit allocation and quantisation are always fp64 + integer.
-template <int N, typename T>
-__device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const T* fx, int shape, bool cur,
-                            bool lastOrNext, bool sbr, int* bpos, int* err) {
-    constexpr int H = N / 2, Q = N / 4;
+// Steps (4)-(7) of a frame: bit allocation, quantisation, header and payload merge.  One copy
+// shared by the long and short instantiations of every precision (not inlined: the two encoders
+// are instruction-cache bound otherwise).  flags: 1 long frame, 2 SBR, 4 transient block,
+// 8 last-or-next-transient.  S.lines holds the scaled MDCT lines, S.smr the SMRs, S.env the SBR sums.
+static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, unsigned char* raw, EncLog lg, int flags,
+                                               int scale, int* bpos, int* err) {
+    EncSmem S;
+    enc_smem_carve(raw, S);
+    S.logVal = lg.val; S.logW = lg.w; S.logCnt = lg.cnt; S.logCap = lg.cap;
+    const bool isLong = flags & 1, sbr = flags & 2, cur = flags & 4, lastOrNext = flags & 8;
+    const int H = isLong ? PAC_HALF_LONG : PAC_HALF_SHORT;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
+    const PacBands& bands = isLong ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
-    const PsyConst<T> pc = psy_const<N, T>(dev);
-    const PacTables<T>& tabsT = psy_tabs<T>(dev);
-    const T* winTab = (N == PAC_NLONG) ? tabsT.win_long : tabsT.win_short;
-    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(N == PAC_NLONG ? tabsT.tw_mdct_long : tabsT.tw_mdct_short);
-    const cplx<T>* rootsQ = reinterpret_cast<const cplx<T>*>(tabsT.tw_fft[N == PAC_NLONG ? 2 : 0]);
-    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(S.fb);
-    T* mkT = reinterpret_cast<T*>(S.mk);
-
-    PHASE_T0();
-    // (1) window + MDCT (coder/codec.py:301-305)
-    mdct_fold<T, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
-    __syncthreads();
-    cta_fft<T, Q, 1, ENC_NT>(fbuf, rootsQ, tid);
-    mdct_post<T, N, 1, ENC_NT, double>(fbuf, tw, (T)2 / (T)N, S.lines, tid);
-    __syncthreads();
-    double mx = 0.0;
-    for (int i = tid; i < H; i += ENC_NT) mx = fmax(mx, fabs(S.lines[i]));
-    double maxLine = block_max(mx, S.red, tid);
-
-    PHASE(0);
-    // (2) Hann FFT magnitude (shared by the psychoacoustic model and the SBR envelope)
-    hann_rfft_mag<N, ENC_NT, T>(fx, pc, fbuf, mkT, tid);
-    if (sbr) {                                    // coder/codec.py:460-473
-        double m2 = 0.0;
-        for (int k = tid; k <= H; k += ENC_NT) m2 = fmax(m2, (double)mkT[k]);
-        double maxFFT = block_max(m2, S.red, tid) / (double)H;
-        maxLine = fmax(maxLine, maxFFT);
-        // per omitted band: sum of fftLines = |X|/H over the band (scale applied later, exact)
-        for (int b = warp; b < nB; b += ENC_NT / 32) {
-            if (!bands.omitted[b]) continue;
-            double a = 0.0;
-            for (int i = lane; i < bands.nLines[b]; i += 32) a += (double)mkT[bands.lower[b] + i] / (double)H;
-            a = warp_sum(a);
-            if (lane == 0) S.env[b] = a;
-        }
-        __syncthreads();
-    }
-    const int scale = scale_factor(maxLine, dev->nScaleBits, 5);      // codec.py:308-311 (default nMantBits)
     const double up = (double)(1 << scale);
-    for (int i = tid; i < H; i += ENC_NT) S.lines[i] *= up;
-    for (int k = tid; k <= H; k += ENC_NT) {
-        T m = mkT[k];
-        mkT[k] = pc.norm * (m * m);
-    }
-    __syncthreads();
-
-    PHASE(1);
-    // (3) psychoacoustic model -> SMR per band
-    const MaskerList<T> ml = masker_list<T>(reinterpret_cast<T*>(S.fb));
-    const int nMask = pick_maskers<N, ENC_NT, T>(mkT, pc, ml, tid);
-    masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mkT, tid);
-    band_smr<ENC_NT, T>(S.lines, scale, mkT, bands, S.smr, tid);
-
-    PHASE(2);
     // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)
     if (tid < nB) S.nlEff[tid] = (sbr && bands.omitted[tid]) ? 1 : bands.nLines[tid];
     __syncthreads();
@@ -207,17 +159,17 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
         }
         S.wordOff[nB] = w;
         S.capOff[nB] = c;
-        if (w > BAND_WORDS || c > (N == PAC_NLONG ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
+        if (w > BAND_WORDS || c > (isLong ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
     }
     for (int i = tid; i < BAND_WORDS; i += ENC_NT) S.bandbits[i] = 0u;
     __syncthreads();
-    if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (N == PAC_NLONG ? 2048 : 256)) return 0;
+    if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (isLong ? 2048 : 256)) return 0;
     PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
     int* yws = reinterpret_cast<int*>(S.mk);              // masked threshold is dead from here on
     // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
     // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
-    double* wsA = (N == PAC_NLONG) ? S.xs : S.lines + 256;
-    double* wsB = (N == PAC_NLONG) ? S.fb : S.lines + 512;
+    double* wsA = isLong ? S.xs : S.lines + 256;
+    double* wsB = isLong ? S.fb : S.lines + 512;
     if (dev->useVQ) {
         // roots: one warp per band: gain, normalised copy of the band, root node of its split tree
         if (tid == 0) S.misc[6] = 0;
@@ -351,3 +303,74 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     return S.misc[2];
 }
 
+
+// Encode one frame of N samples at fx (shared) and append its fields to the block
+// bitstream at bit position *bpos.  Returns the DECLARED size in bits
+// (getNumBytesNeeded, coder/pacfile.py:342-361).  sbr: long frame of an SBR stream.
+// T: arithmetic of the transform and psychoacoustic stages (double = parity path, float = fast
+// path); bit allocation and quantisation are always fp64 + integer.
+template <int N, typename T>
+__device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const T* fx, int shape, bool cur,
+                            bool lastOrNext, bool sbr, int* bpos, int* err) {
+    constexpr int H = N / 2, Q = N / 4;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
+    const int nB = bands.nBands;
+    const PsyConst<T> pc = psy_const<N, T>(dev);
+    const PacTables<T>& tabsT = psy_tabs<T>(dev);
+    const T* winTab = (N == PAC_NLONG) ? tabsT.win_long : tabsT.win_short;
+    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(N == PAC_NLONG ? tabsT.tw_mdct_long : tabsT.tw_mdct_short);
+    const cplx<T>* rootsQ = reinterpret_cast<const cplx<T>*>(tabsT.tw_fft[N == PAC_NLONG ? 2 : 0]);
+    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(S.fb);
+    T* mkT = reinterpret_cast<T*>(S.mk);
+
+    PHASE_T0();
+    // (1) window + MDCT (coder/codec.py:301-305)
+    mdct_fold<T, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
+    __syncthreads();
+    cta_fft<T, Q, 1, ENC_NT>(fbuf, rootsQ, tid);
+    mdct_post<T, N, 1, ENC_NT, double>(fbuf, tw, (T)2 / (T)N, S.lines, tid);
+    __syncthreads();
+    double mx = 0.0;
+    for (int i = tid; i < H; i += ENC_NT) mx = fmax(mx, fabs(S.lines[i]));
+    double maxLine = block_max(mx, S.red, tid);
+
+    PHASE(0);
+    // (2) Hann FFT magnitude (shared by the psychoacoustic model and the SBR envelope)
+    hann_rfft_mag<N, ENC_NT, T>(fx, pc, fbuf, mkT, tid);
+    if (sbr) {                                    // coder/codec.py:460-473
+        double m2 = 0.0;
+        for (int k = tid; k <= H; k += ENC_NT) m2 = fmax(m2, (double)mkT[k]);
+        double maxFFT = block_max(m2, S.red, tid) / (double)H;
+        maxLine = fmax(maxLine, maxFFT);
+        // per omitted band: sum of fftLines = |X|/H over the band (scale applied later, exact)
+        for (int b = warp; b < nB; b += ENC_NT / 32) {
+            if (!bands.omitted[b]) continue;
+            double a = 0.0;
+            for (int i = lane; i < bands.nLines[b]; i += 32) a += (double)mkT[bands.lower[b] + i] / (double)H;
+            a = warp_sum(a);
+            if (lane == 0) S.env[b] = a;
+        }
+        __syncthreads();
+    }
+    const int scale = scale_factor(maxLine, dev->nScaleBits, 5);      // codec.py:308-311 (default nMantBits)
+    const double up = (double)(1 << scale);
+    for (int i = tid; i < H; i += ENC_NT) S.lines[i] *= up;
+    for (int k = tid; k <= H; k += ENC_NT) {
+        T m = mkT[k];
+        mkT[k] = pc.norm * (m * m);
+    }
+    __syncthreads();
+
+    PHASE(1);
+    // (3) psychoacoustic model -> SMR per band
+    const MaskerList<T> ml = masker_list<T>(reinterpret_cast<T*>(S.fb));
+    const int nMask = pick_maskers<N, ENC_NT, T>(mkT, pc, ml, tid);
+    masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mkT, tid);
+    band_smr<ENC_NT, T>(S.lines, scale, mkT, bands, S.smr, tid);
+
+    PHASE(2);
+    const int flags = (N == PAC_NLONG ? 1 : 0) | (sbr ? 2 : 0) | (cur ? 4 : 0) | (lastOrNext ? 8 : 0);
+    const EncLog lg = {S.logVal, S.logW, S.logCnt, S.logCap};
+    return encode_back(dev, S.raw, lg, flags, scale, bpos, err);
+}

@@ -81,3 +81,19 @@ static __device__ __forceinline__ int pac_fft_index(int n) {
 }
 
 #define PAC_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return -(int)e_ - 1000; } while (0)
+
+// fp64 transcendentals, one out-of-line copy each: CUDA's double-precision log10 / atan / pow ...
+// expand to 1-3 KB of SASS per call site and the frame kernels are instruction-cache bound.
+// Same code as the inlined form, so results are bit-identical.  The float overloads stay inline.
+#ifdef __CUDACC__
+static __device__ __noinline__ double pm_log10(double x) { return log10(x); }
+static __device__ __noinline__ double pm_log2(double x) { return log2(x); }
+static __device__ __noinline__ double pm_log(double x) { return log(x); }
+static __device__ __noinline__ double pm_atan(double x) { return atan(x); }
+static __device__ __noinline__ double pm_tan(double x) { return tan(x); }
+static __device__ __noinline__ double pm_pow(double x, double y) { return pow(x, y); }
+static __device__ __noinline__ void pm_sincos(double x, double* s, double* c) { *s = sin(x); *c = cos(x); }
+static __device__ __forceinline__ float pm_log10(float x) { return log10f(x); }
+static __device__ __forceinline__ float pm_atan(float x) { return atanf(x); }
+static __device__ __forceinline__ float pm_pow(float x, float y) { return powf(x, y); }
+#endif

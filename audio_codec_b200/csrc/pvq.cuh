@@ -236,7 +236,7 @@ __device__ __forceinline__ int warp_quantize_gain_shape(const PvqTab& t, const d
         bg += bs - used;
         total = used;
     }
-    double g = log(1.0 + 255.0 * (gain / (double)L)) / log(256.0);      // mu_law_fn
+    double g = pm_log(1.0 + 255.0 * (gain / (double)L)) / log(256.0);      // mu_law_fn
     if (bg < 0) bg = 0;
     if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
     unsigned long long gi = quantize_uniform(g, bg);
@@ -274,7 +274,7 @@ struct BandEnc {
 
 // np.add.reduce of |a[i]| in NumPy's pairwise order (loops_utils.h.src pairwise_sum): blocks of at
 // most 128 elements are summed with 8 accumulators, larger arrays are halved recursively.
-__device__ __forceinline__ double np_abs_sum_block(const double* a, int n) {
+static __device__ __noinline__ double np_abs_sum_block(const double* a, int n) {
     if (n < 8) {
         double r = 0.0;
         for (int i = 0; i < n; ++i) r += fabs(a[i]);
@@ -443,7 +443,7 @@ __device__ __forceinline__ int thread_layout_band(TNode* nodes, const BandEnc& b
         }
     }
     int bg = be.bg + (be.bs != 0 ? be.bs - (pos - bit0) : 0);
-    const double g = log(1.0 + 255.0 * (be.gain / (double)be.L)) / log(256.0);      // mu_law_fn
+    const double g = pm_log(1.0 + 255.0 * (be.gain / (double)be.L)) / log(256.0);      // mu_law_fn
     if (bg < 0) bg = 0;
     if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
     const unsigned long long gi = quantize_uniform(g, bg);

@@ -133,7 +133,7 @@ __device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR
     double gq = dequantize_uniform(gi, bg);
     // inv_mu_law_fn: sign(y)/mu * ((1+mu)^|y| - 1)
     double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
-    double gain = sg / 255.0 * (pow(256.0, fabs(gq)) - 1.0) * (double)L;
+    double gain = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;
     for (int i = lane; i < L; i += 32) out[i] = gain * wsA[i];
     __syncwarp();
 }
@@ -233,7 +233,7 @@ __device__ __forceinline__ void warp_parse_gain_shape(const PvqTab& t, BitR& br,
     const double gq = dequantize_uniform(gi, bg);
     const double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
     if (lane == 0) {
-        bd->gain = sg / 255.0 * (pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
+        bd->gain = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
         bd->tail = tail;
         bd->L = L;
     }

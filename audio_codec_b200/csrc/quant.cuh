@@ -108,24 +108,30 @@ struct BitR {
     long long pos;            // bit cursor
     long long end;            // total bits available
 };
-// Next n (<= 64) bits, MSB first; bits past `end` (a whole number of bytes) read as 0.
-__device__ __forceinline__ unsigned long long br_get(BitR& r, int n) {
-    if (n <= 0) return 0ull;
-    const long long pos = r.pos;
-    r.pos = pos + n;
-    const long long byte = pos >> 3, endByte = r.end >> 3;
+// n (1..64) bits at bit position pos, MSB first; bits past `end` (a whole number of bytes) read as 0.
+// Out of line (one copy per kernel: the byte loop is ~1 KB of SASS per call site) and pure, so the
+// cursor struct of the caller stays in registers.
+static __device__ __noinline__ unsigned long long br_peek(const unsigned char* p, long long pos, long long end, int n) {
+    const long long byte = pos >> 3, endByte = end >> 3;
     const int off = (int)(pos & 7);
     const int nb = (off + n + 7) >> 3;               // bytes touched, <= 9
     unsigned long long hi = 0ull;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        unsigned b = (i < nb && byte + i < endByte) ? r.p[byte + i] : 0u;
+        unsigned b = (i < nb && byte + i < endByte) ? p[byte + i] : 0u;
         hi = (hi << 8) | b;
     }
     unsigned long long v = hi << off;
     if (nb == 9) {
-        unsigned b8 = (byte + 8 < endByte) ? r.p[byte + 8] : 0u;
+        unsigned b8 = (byte + 8 < endByte) ? p[byte + 8] : 0u;
         v |= (unsigned long long)(b8 >> (8 - off));
     }
     return n == 64 ? v : v >> (64 - n);
+}
+// Next n (<= 64) bits of the stream.
+__device__ __forceinline__ unsigned long long br_get(BitR& r, int n) {
+    if (n <= 0) return 0ull;
+    const long long pos = r.pos;
+    r.pos = pos + n;
+    return br_peek(r.p, pos, r.end, n);
 }
