@@ -161,7 +161,7 @@ static int launch_inv_stream(pac_ctx* ctx, const void* X, int nRows, int nFrames
     const int grid = (int)std::min<long long>(148, (units + W - 1) / W);
     const int vec = aligned16(X) && aligned16(y) && (rowStride * sizeof(T)) % 16 == 0;
     auto kern = k_imdct_ola_stream<T>;
-    const size_t smem = ms_smem_bytes<T>();
+    const size_t smem = ms_inv_smem_bytes<T>();
     PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<grid, W * 32, smem, st>>>((const T*)X, nFrames, seg, segs, units, win,
                                       reinterpret_cast<const cplx<T>*>(t.tw_mdct_long),

@@ -2,61 +2,72 @@
 // warp pipelines.  Each warp walks a run of consecutive frames of one (stream, channel) row and
 // keeps everything it needs on chip:
 //   * a frame is two 1024-sample blocks; consecutive frames share one, so a warp fetches every
-//     PCM block from HBM exactly once (one halo block per run), with the NEXT block already in
-//     flight in registers while the current frame is transformed (16-byte coalesced loads);
-//   * the N/4 = 512-point complex FFT is three radix-8 Stockham passes inside the warp's own
-//     shared-memory tile, synchronised with __syncwarp only - there is no CTA-wide barrier in
+//     block from HBM exactly once (one halo block per run), with the NEXT block already in flight
+//     in registers while the current frame is transformed (16-byte coalesced loads);
+//   * the N/4 = 512-point complex FFT is 16 x 16 x 2: a lane owns 16 points of stride 32, so the
+//     fold / pre-twiddle output feeds the first radix-16 butterfly straight from registers, ONE
+//     shared-memory exchange (skewed, conflict-free both ways) feeds the second, and the last
+//     radix-2 pairs lane l with lane l^16 through shuffles.  __syncwarp only - no CTA barrier in
 //     the steady state, so warps drift apart and hide each other's latency;
-//   * window, twiddles and FFT roots sit in shared memory once per CTA;
+//   * samples and window are kept de-interleaved (even / odd index arrays) in shared memory:
+//     every fold, post-twiddle and read-out access is then unit-stride across the warp;
 //   * results leave as 16-byte coalesced stores.
 // Algorithmic HBM traffic: one read and one write of 1024 values per channel-frame.
+// Shared-memory wavefronts per frame (fp32): ~450 (previous radix-8 x 3 tile version: 1025).
 #pragma once
 #include "mdct.cuh"
 
-#define MS_PAD(i) ((i) + ((i) >> 3))        // skew against bank conflicts of the strided Stockham writes
+#define MS_SKEW(p) ((p) + ((p) >> 5))            // exchange tile: p = 16 l + r (write) and l + 32 r (read) conflict-free
+#define MS_OSK(k) ((k) + (((k) >> 8) << 4))      // staging arrays: k = (l & 15) + 16 r + 256 (l >> 4) conflict-free
+#define MS_TILE 528                              // 512 + skew
 
 template <typename T> struct MsCfg;
 template <> struct MsCfg<float> { static constexpr int WARPS = 16; };
-template <> struct MsCfg<double> { static constexpr int WARPS = 7; };   // 32 KB tables + 7 x 25.6 KB <= 227 KB
+template <> struct MsCfg<double> { static constexpr int WARPS = 7; };
 
-// Q-point FFT of the warp's padded tile (Q = 512: three radix-8 passes).
-template <typename T, int Q>
-__device__ __forceinline__ void warp_fft512(cplx<T>* fb, const cplx<T>* __restrict__ roots, int lane) {
-    static_assert(Q == 512, "three radix-8 passes");
-    constexpr int J = Q / 8;                 // butterflies per pass
+// 16-point DFT in registers, natural order in and out (4 x 4 Cooley-Tukey).
+template <typename T> __device__ __forceinline__ void bfly16(cplx<T>* u) {
+    const T h = (T)0.70710678118654752440, c1 = (T)0.92387953251128675613, s1 = (T)0.38268343236508977173;
+    cplx<T> a[4][4];
 #pragma unroll
-    for (int pass = 0; pass < 3; ++pass) {
-        const int Ns = pass == 0 ? 1 : (pass == 1 ? 8 : 64);
-        cplx<T> u[2][8];
+    for (int r0 = 0; r0 < 4; ++r0) {
+        cplx<T> t[4] = {u[r0], u[4 + r0], u[8 + r0], u[12 + r0]};
+        bfly4(t);
 #pragma unroll
-        for (int it = 0; it < 2; ++it) {
-            const int j = lane + it * 32;
-            const int k = j & (Ns - 1);
-            const int step = k * (Q / (Ns * 8));
-#pragma unroll
-            for (int r = 0; r < 8; ++r) {
-                cplx<T> v = fb[MS_PAD(r * J + j)];
-                if (r > 0 && pass > 0) v = cmul(v, roots[r * step]);
-                u[it][r] = v;
-            }
-            bfly8(u[it]);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int it = 0; it < 2; ++it) {
-            const int j = lane + it * 32;
-            const int k = j & (Ns - 1);
-            const int base = (j - k) * 8 + k;
-#pragma unroll
-            for (int r = 0; r < 8; ++r) fb[MS_PAD(base + r * Ns)] = u[it][r];
-        }
-        __syncwarp();
+        for (int k1 = 0; k1 < 4; ++k1) a[r0][k1] = t[k1];
     }
-    (void)J;
+    const cplx<T> w1 = {c1, -s1}, w2 = {h, -h}, w3 = {s1, -c1}, w6 = {-h, -h}, w9 = {-c1, s1};
+    a[1][1] = cmul(a[1][1], w1); a[1][2] = cmul(a[1][2], w2); a[1][3] = cmul(a[1][3], w3);
+    a[2][1] = cmul(a[2][1], w2); a[2][2] = cmnj(a[2][2]);     a[2][3] = cmul(a[2][3], w6);
+    a[3][1] = cmul(a[3][1], w3); a[3][2] = cmul(a[3][2], w6); a[3][3] = cmul(a[3][3], w9);
+#pragma unroll
+    for (int k1 = 0; k1 < 4; ++k1) {
+        cplx<T> t[4] = {a[0][k1], a[1][k1], a[2][k1], a[3][k1]};
+        bfly4(t);
+#pragma unroll
+        for (int k2 = 0; k2 < 4; ++k2) u[k1 + 4 * k2] = t[k2];
+    }
 }
+
+// PER/2 consecutive values of an array (one 8-byte access for either type).
+template <typename T> struct MsRun;
+template <> struct MsRun<float> {
+    static constexpr int L = 2;
+    static __device__ __forceinline__ void ld(const float* p, float* o) {
+        float2 v = *reinterpret_cast<const float2*>(p);
+        o[0] = v.x; o[1] = v.y;
+    }
+    static __device__ __forceinline__ void st(float* p, const float* o) { *reinterpret_cast<float2*>(p) = make_float2(o[0], o[1]); }
+};
+template <> struct MsRun<double> {
+    static constexpr int L = 1;
+    static __device__ __forceinline__ void ld(const double* p, double* o) { o[0] = *p; }
+    static __device__ __forceinline__ void st(double* p, const double* o) { *p = o[0]; }
+};
 
 template <typename T> struct MsBlock {        // one 1024-value block in registers, 16 bytes per access
     static constexpr int NV = 1024 * sizeof(T) / 16 / 32;
+    static constexpr int PER = 16 / sizeof(T);
     uint4 v[NV];
     __device__ __forceinline__ void load(const T* __restrict__ src, int lane, bool vec) {
         if (vec) {
@@ -64,7 +75,6 @@ template <typename T> struct MsBlock {        // one 1024-value block in registe
 #pragma unroll
             for (int i = 0; i < NV; ++i) v[i] = __ldg(p + i * 32 + lane);
         } else {
-            constexpr int PER = 16 / sizeof(T);
 #pragma unroll
             for (int i = 0; i < NV; ++i) {
                 T t[PER];
@@ -74,10 +84,18 @@ template <typename T> struct MsBlock {        // one 1024-value block in registe
             }
         }
     }
-    __device__ __forceinline__ void to_smem(T* dst, int lane) const {
-        uint4* p = reinterpret_cast<uint4*>(dst);
+    // de-interleave into E[512] (even indices) and O[512] = E + 512
+    __device__ __forceinline__ void to_smem_eo(T* E, int lane) const {
+        constexpr int L = MsRun<T>::L;
 #pragma unroll
-        for (int i = 0; i < NV; ++i) p[i * 32 + lane] = v[i];
+        for (int i = 0; i < NV; ++i) {
+            const T* t = reinterpret_cast<const T*>(&v[i]);
+            T ev[L], ov[L];
+#pragma unroll
+            for (int q = 0; q < L; ++q) { ev[q] = t[2 * q]; ov[q] = t[2 * q + 1]; }
+            MsRun<T>::st(E + (i * 32 + lane) * L, ev);
+            MsRun<T>::st(E + 512 + (i * 32 + lane) * L, ov);
+        }
     }
     __device__ __forceinline__ void zero() {
 #pragma unroll
@@ -85,42 +103,72 @@ template <typename T> struct MsBlock {        // one 1024-value block in registe
     }
 };
 
-template <typename T>
-__device__ __forceinline__ void ms_store_block(T* __restrict__ dst, const T* src, int lane, bool vec) {
-    constexpr int NV = 1024 * sizeof(T) / 16 / 32;
-    if (vec) {
-        const uint4* s = reinterpret_cast<const uint4*>(src);
-        uint4* d = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-        for (int i = 0; i < NV; ++i) d[i * 32 + lane] = s[i * 32 + lane];
-    } else {
-        for (int i = lane; i < 1024; i += 32) dst[i] = src[i];
-    }
-}
-
-// CTA-shared tables: window [N] (if any), MDCT twiddles [Q], FFT roots [Q].
+// CTA-shared tables.  win: [2048] either natural order (inverse) or de-interleaved per block
+// (forward: [(block * 2 + odd) * 512 + i] = w[block * 1024 + 2 i + odd]); tw: MDCT twiddles [512];
+// r1: second-pass roots [r * 16 + k] = exp(-2 pi j 2 r k / 512); roots: exp(-2 pi j k / 512).
 template <typename T> struct MsTables {
     T* win;
     cplx<T>* tw;
+    cplx<T>* r1;
     cplx<T>* roots;
 };
-template <typename T, int N, int NT>
+template <typename T, int NT, bool EO>
 __device__ __forceinline__ unsigned char* ms_load_tables(unsigned char* raw, const T* __restrict__ winG,
                                                          const cplx<T>* __restrict__ twG,
                                                          const cplx<T>* __restrict__ rootsG, MsTables<T>& t) {
-    constexpr int Q = N / 4;
+    constexpr int N = 2048, Q = 512;
     t.win = reinterpret_cast<T*>(raw);
     t.tw = reinterpret_cast<cplx<T>*>(t.win + N);
-    t.roots = t.tw + Q;
-    for (int i = threadIdx.x; i < N; i += NT) t.win[i] = winG ? winG[i] : (T)1;
-    for (int i = threadIdx.x; i < Q; i += NT) { t.tw[i] = twG[i]; t.roots[i] = rootsG[i]; }
+    t.r1 = t.tw + Q;
+    t.roots = t.r1 + 256;
+    for (int i = threadIdx.x; i < N; i += NT) {
+        const T w = winG ? winG[i] : (T)1;
+        if (EO) t.win[((i >> 10) * 2 + (i & 1)) * 512 + ((i & 1023) >> 1)] = w;
+        else t.win[i] = w;
+    }
+    for (int i = threadIdx.x; i < Q; i += NT) t.tw[i] = twG[i];
+    for (int i = threadIdx.x; i < 256; i += NT) {
+        t.roots[i] = rootsG[i];
+        t.r1[i] = rootsG[(2 * (i >> 4) * (i & 15)) & (Q - 1)];
+    }
     __syncthreads();
-    return reinterpret_cast<unsigned char*>(t.roots + Q);
+    return reinterpret_cast<unsigned char*>(t.roots + 256);
 }
 
 template <typename T> __host__ __device__ constexpr size_t ms_smem_bytes() {
-    // tables (N + 2*2*Q values) + per warp: two blocks (2*M) + padded FFT tile (2*(Q + Q/8))
-    return sizeof(T) * ((size_t)2048 + 4 * 512 + (size_t)MsCfg<T>::WARPS * (2 * 1024 + 2 * (512 + 64)));
+    // tables (2048 + 2 * (512 + 256 + 256) values) + per warp: two blocks (2048) + exchange tile (2 * MS_TILE)
+    return sizeof(T) * ((size_t)2048 + 2 * 1024 + (size_t)MsCfg<T>::WARPS * (2048 + 2 * MS_TILE));
+}
+
+// 512-point FFT of z[lane + 32 i] = u[i]; on return u[r] = Z[(lane & 15) + 16 r + 256 (lane >> 4)].
+// The tile is free again when the function returns.
+template <typename T>
+__device__ __forceinline__ void warp_fft512(cplx<T>* u, T* tileRe, T* tileIm, const MsTables<T>& tb, int lane) {
+    bfly16(u);
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        tileRe[MS_SKEW(16 * lane + r)] = u[r].x;
+        tileIm[MS_SKEW(16 * lane + r)] = u[r].y;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        u[r].x = tileRe[MS_SKEW(lane + 32 * r)];
+        u[r].y = tileIm[MS_SKEW(lane + 32 * r)];
+    }
+    __syncwarp();
+    const int k = lane & 15;
+#pragma unroll
+    for (int r = 1; r < 16; ++r) u[r] = cmul(u[r], tb.r1[r * 16 + k]);
+    bfly16(u);
+    const bool lo = lane < 16;
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        cplx<T> o = {__shfl_xor_sync(0xffffffffu, u[r].x, 16), __shfl_xor_sync(0xffffffffu, u[r].y, 16)};
+        const cplx<T> a = lo ? u[r] : o, b = lo ? o : u[r];
+        const cplx<T> wb = cmul(b, tb.roots[k + 16 * r]);
+        u[r] = lo ? cadd(a, wb) : csub(a, wb);
+    }
 }
 
 // ---------------------------------------------------------------- forward
@@ -130,14 +178,15 @@ __global__ void __launch_bounds__(MsCfg<T>::WARPS * 32, 1)
 k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int seg, int segsPerRow, long long nUnits,
                   const T* __restrict__ winG, const cplx<T>* __restrict__ twG, const cplx<T>* __restrict__ rootsG,
                   T* __restrict__ out, int vec) {
-    constexpr int N = 2048, M = 1024, Q = 512, QP = Q + Q / 8, W = MsCfg<T>::WARPS;
+    constexpr int N = 2048, M = 1024, Q = 512, H = Q / 2, W = MsCfg<T>::WARPS;
+    constexpr int NV = MsBlock<T>::NV, PER = MsBlock<T>::PER, L = MsRun<T>::L;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     MsTables<T> tb;
-    unsigned char* p = ms_load_tables<T, N, W * 32>(smem_raw, winG, twG, rootsG, tb);
+    unsigned char* p = ms_load_tables<T, W * 32, true>(smem_raw, winG, twG, rootsG, tb);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    T* blk = reinterpret_cast<T*>(p) + (size_t)warp * (2 * M + 2 * QP);
-    cplx<T>* fb = reinterpret_cast<cplx<T>*>(blk + 2 * M);
-    const bool useWin = winG != nullptr;
+    T* blk = reinterpret_cast<T*>(p) + (size_t)warp * (2 * M + 2 * MS_TILE);   // [2][E 512 | O 512]
+    T* tileRe = blk + 2 * M;
+    T* tileIm = tileRe + MS_TILE;
     const T scale = (T)2 / (T)N;
     for (long long unit = (long long)blockIdx.x * W + warp; unit < nUnits; unit += (long long)gridDim.x * W) {
         const long long row = unit / segsPerRow;
@@ -146,43 +195,59 @@ k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int
         T* dst = out + (row * nFrames + f0) * M;
         MsBlock<T> pre;
         pre.load(src, lane, vec);
-        pre.to_smem(blk, lane);
+        pre.to_smem_eo(blk, lane);
         pre.load(src + M, lane, vec);
         for (int f = f0; f < f1; ++f) {
             const int cur = (f - f0) & 1;
-            T* b0 = blk + cur * M;           // samples [0, M) of the frame
-            T* b1 = blk + (cur ^ 1) * M;     // samples [M, N)
-            pre.to_smem(b1, lane);
+            const T* E0 = blk + cur * M;         // samples [0, M) of the frame, even / odd indices
+            const T* E1 = blk + (cur ^ 1) * M;   // samples [M, N)
+            const T* W0 = tb.win;
+            const T* W1 = tb.win + M;
+            pre.to_smem_eo(blk + (cur ^ 1) * M, lane);
             __syncwarp();
             if (f + 1 < f1) pre.load(src + (long long)(f - f0 + 2) * M, lane, vec);
-            // fold + window + pre-twiddle (mdct_fold, one frame)
-#pragma unroll 4
-            for (int n = lane; n < Q; n += 32) {
-                int i0, i1, i2, i3;
-                T re, im;
-                if (2 * n < Q) {
-                    i0 = 3 * Q - 1 - 2 * n; i1 = 3 * Q + 2 * n; i2 = Q - 1 - 2 * n; i3 = Q + 2 * n;
+            // fold + window + pre-twiddle (mdct_fold): every access is unit stride across the warp
+            cplx<T> u[16];
+#pragma unroll
+            for (int it = 0; it < 16; ++it) {
+                const int n = lane + 32 * it;
+                cplx<T> t;
+                if (it < 8) {
+                    const int a = H - 1 - n, b = H + n;
+                    const T a0 = E1[512 + a] * W1[512 + a], a1 = E1[b] * W1[b];
+                    const T a2 = E0[512 + a] * W0[512 + a], a3 = E0[b] * W0[b];
+                    t.x = -a0 - a1; t.y = a2 - a3;
                 } else {
-                    i0 = 2 * n - Q; i1 = 3 * Q - 1 - 2 * n; i2 = Q + 2 * n; i3 = 5 * Q - 1 - 2 * n;
+                    const int a = n - H, b = 3 * H - 1 - n;
+                    const T a0 = E0[a] * W0[a], a1 = E0[512 + b] * W0[512 + b];
+                    const T a2 = E1[a] * W1[a], a3 = E1[512 + b] * W1[512 + b];
+                    t.x = a0 - a1; t.y = -a2 - a3;
                 }
-                T a0 = i0 < M ? b0[i0] : b1[i0 - M], a1 = i1 < M ? b0[i1] : b1[i1 - M];
-                T a2 = i2 < M ? b0[i2] : b1[i2 - M], a3 = i3 < M ? b0[i3] : b1[i3 - M];
-                if (useWin) { a0 *= tb.win[i0]; a1 *= tb.win[i1]; a2 *= tb.win[i2]; a3 *= tb.win[i3]; }
-                if (2 * n < Q) { re = -a0 - a1; im = a2 - a3; } else { re = a0 - a1; im = -a2 - a3; }
-                cplx<T> t = {re, im};
-                fb[MS_PAD(n)] = cmul(t, tb.tw[n]);
+                u[it] = cmul(t, tb.tw[n]);
+            }
+            warp_fft512<T>(u, tileRe, tileIm, tb, lane);
+            // post-twiddle into the staging arrays (even / odd output indices)
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+                const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
+                const cplx<T> y = cmul(u[r], tb.tw[k]);
+                tileRe[MS_OSK(k)] = scale * y.x;               // out[2k]
+                tileIm[MS_OSK(Q - 1 - k)] = -scale * y.y;      // out[M - 1 - 2k]
             }
             __syncwarp();
-            warp_fft512<T, Q>(fb, tb.roots, lane);
-            // post-twiddle into the (now dead) first block, natural order
-#pragma unroll 4
-            for (int k = lane; k < Q; k += 32) {
-                cplx<T> y = cmul(fb[MS_PAD(k)], tb.tw[k]);
-                b0[2 * k] = scale * y.x;
-                b0[M - 1 - 2 * k] = -scale * y.y;
+            T* d = dst + (long long)(f - f0) * M;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const int v = i * 32 + lane;
+                T ev[L], ov[L], o[PER];
+                MsRun<T>::ld(tileRe + MS_OSK(v * L), ev);
+                MsRun<T>::ld(tileIm + MS_OSK(v * L), ov);
+#pragma unroll
+                for (int q = 0; q < L; ++q) { o[2 * q] = ev[q]; o[2 * q + 1] = ov[q]; }
+                if (vec) *reinterpret_cast<uint4*>(d + v * PER) = *reinterpret_cast<uint4*>(o);
+                else
+                    for (int e = 0; e < PER; ++e) d[v * PER + e] = o[e];
             }
-            __syncwarp();
-            ms_store_block<T>(dst + (long long)(f - f0) * M, b0, lane, vec);
             __syncwarp();
         }
     }
@@ -191,19 +256,26 @@ k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int
 // ---------------------------------------------------------------- inverse + window + overlap-add
 // unit = (row, run of `seg` output blocks); a row has nFrames + 1 output blocks:
 // block b = w[M:] * imdct(frame b-1)[M:] + w[:M] * imdct(frame b)[:M]  (coder/pacfile.py:289-295).
+// The windowed second half of the previous frame stays in registers (each lane re-reads exactly
+// the positions it wrote).
+template <typename T> __host__ __device__ constexpr size_t ms_inv_smem_bytes() {
+    return sizeof(T) * ((size_t)2048 + 2 * 1024 + (size_t)MsCfg<T>::WARPS * (1024 + 2 * MS_TILE));
+}
+
 template <typename T>
 __global__ void __launch_bounds__(MsCfg<T>::WARPS * 32, 1)
 k_imdct_ola_stream(const T* __restrict__ X, int nFrames, int seg, int segsPerRow, long long nUnits,
                    const T* __restrict__ winG, const cplx<T>* __restrict__ twG, const cplx<T>* __restrict__ rootsG,
                    T* __restrict__ y, long long rowStride, int vec) {
-    constexpr int N = 2048, M = 1024, Q = 512, QP = Q + Q / 8, W = MsCfg<T>::WARPS;
+    constexpr int M = 1024, Q = 512, W = MsCfg<T>::WARPS;
+    constexpr int NV = MsBlock<T>::NV, PER = MsBlock<T>::PER, L = MsRun<T>::L;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     MsTables<T> tb;
-    unsigned char* p = ms_load_tables<T, N, W * 32>(smem_raw, winG, twG, rootsG, tb);
+    unsigned char* p = ms_load_tables<T, W * 32, false>(smem_raw, winG, twG, rootsG, tb);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    T* xv = reinterpret_cast<T*>(p) + (size_t)warp * (2 * M + 2 * QP);   // coefficients, then DCT-IV output
-    T* tail = xv + M;                                                     // windowed second half of the previous frame
-    cplx<T>* fb = reinterpret_cast<cplx<T>*>(xv + 2 * M);
+    T* Ei = reinterpret_cast<T*>(p) + (size_t)warp * (M + 2 * MS_TILE);   // coefficients: even | odd indices
+    T* Ev = Ei + M;                                                        // DCT-IV output, even indices (skewed)
+    T* Ov = Ev + MS_TILE;                                                  // odd indices
     const int nOutRow = nFrames + 1;
     for (long long unit = (long long)blockIdx.x * W + warp; unit < nUnits; unit += (long long)gridDim.x * W) {
         const long long row = unit / segsPerRow;
@@ -211,57 +283,80 @@ k_imdct_ola_stream(const T* __restrict__ X, int nFrames, int seg, int segsPerRow
         const T* src = X + row * (long long)nFrames * M;
         T* dst = y + row * rowStride;
         MsBlock<T> pre;
+        T tail[NV * PER];
+#pragma unroll
+        for (int i = 0; i < NV * PER; ++i) tail[i] = (T)0;
         // frames b0-1 (halo: only its tail is needed) .. b1-1
         int f = b0 - 1;
         if (f >= 0) pre.load(src + (long long)f * M, lane, vec); else pre.zero();
         for (; f < b1; ++f) {
             const bool have = f >= 0 && f < nFrames;
-            pre.to_smem(xv, lane);
+            pre.to_smem_eo(Ei, lane);
             __syncwarp();
             if (f + 1 < b1 && f + 1 < nFrames) pre.load(src + (long long)(f + 1) * M, lane, vec); else pre.zero();
             if (have) {
-#pragma unroll 4
-                for (int n = lane; n < Q; n += 32) {
-                    cplx<T> t = {xv[2 * n], xv[M - 1 - 2 * n]};
-                    fb[MS_PAD(n)] = cmul(t, tb.tw[n]);
+                cplx<T> u[16];
+#pragma unroll
+                for (int it = 0; it < 16; ++it) {
+                    const int n = lane + 32 * it;
+                    const cplx<T> t = {Ei[n], Ei[512 + Q - 1 - n]};      // {X[2n], X[M-1-2n]}
+                    u[it] = cmul(t, tb.tw[n]);
                 }
-                __syncwarp();
-                warp_fft512<T, Q>(fb, tb.roots, lane);
-#pragma unroll 4
-                for (int k = lane; k < Q; k += 32) {
-                    cplx<T> v = cmul(fb[MS_PAD(k)], tb.tw[k]);
-                    xv[2 * k] = v.x;
-                    xv[M - 1 - 2 * k] = -v.y;
+                warp_fft512<T>(u, Ev, Ov, tb, lane);
+#pragma unroll
+                for (int r = 0; r < 16; ++r) {
+                    const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
+                    const cplx<T> v = cmul(u[r], tb.tw[k]);
+                    Ev[MS_OSK(k)] = v.x;                   // xv[2k]
+                    Ov[MS_OSK(Q - 1 - k)] = -v.y;          // xv[M - 1 - 2k]
                 }
-                __syncwarp();
             }
-            // emit output block f (needs tail of f-1 and head of f), then keep this frame's tail
-            constexpr int PER = 16 / sizeof(T), NV = MsBlock<T>::NV;
+            __syncwarp();
+            // emit output block f (tail of f-1 + head of f), then keep this frame's tail
 #pragma unroll
             for (int i = 0; i < NV; ++i) {
                 const int n0 = (i * 32 + lane) * PER;
                 T o[PER], tl[PER];
 #pragma unroll
-                for (int e = 0; e < PER; ++e) {
-                    const int n = n0 + e;
-                    T head = (T)0, tn = (T)0;
-                    if (have) {
-                        head = n < Q ? (T)2 * xv[Q + n] : (T)-2 * xv[3 * Q - 1 - n];          // imdct_sample(v, n)
-                        tn = n < Q ? (T)-2 * xv[Q - 1 - n] : (T)-2 * xv[n - Q];               // imdct_sample(v, M + n)
-                        head *= tb.win[n];
-                        tn *= tb.win[M + n];
+                for (int e = 0; e < PER; ++e) { o[e] = (T)0; tl[e] = (T)0; }
+                if (have) {
+                    T ev[L], ov[L];
+                    if (n0 < Q) {       // head = 2 xv[Q + n], tail = -2 xv[Q - 1 - n]
+                        const int a = (Q + n0) / 2, c = (Q - n0 - PER) / 2;
+                        MsRun<T>::ld(Ev + MS_OSK(a), ev);
+                        MsRun<T>::ld(Ov + MS_OSK(a), ov);
+#pragma unroll
+                        for (int q = 0; q < L; ++q) { o[2 * q] = (T)2 * ev[q]; o[2 * q + 1] = (T)2 * ov[q]; }
+                        MsRun<T>::ld(Ev + MS_OSK(c), ev);
+                        MsRun<T>::ld(Ov + MS_OSK(c), ov);
+#pragma unroll
+                        for (int q = 0; q < L; ++q) { tl[PER - 1 - 2 * q] = (T)-2 * ev[q]; tl[PER - 2 - 2 * q] = (T)-2 * ov[q]; }
+                    } else {            // head = -2 xv[3Q - 1 - n], tail = -2 xv[n - Q]
+                        const int c = (3 * Q - n0 - PER) / 2, a = (n0 - Q) / 2;
+                        MsRun<T>::ld(Ev + MS_OSK(c), ev);
+                        MsRun<T>::ld(Ov + MS_OSK(c), ov);
+#pragma unroll
+                        for (int q = 0; q < L; ++q) { o[PER - 1 - 2 * q] = (T)-2 * ev[q]; o[PER - 2 - 2 * q] = (T)-2 * ov[q]; }
+                        MsRun<T>::ld(Ev + MS_OSK(a), ev);
+                        MsRun<T>::ld(Ov + MS_OSK(a), ov);
+#pragma unroll
+                        for (int q = 0; q < L; ++q) { tl[2 * q] = (T)-2 * ev[q]; tl[2 * q + 1] = (T)-2 * ov[q]; }
                     }
-                    o[e] = (f > b0 - 1 ? tail[n] : (T)0) + head;
-                    tl[e] = tn;
+                    const uint4 w0 = *reinterpret_cast<const uint4*>(tb.win + n0);
+                    const uint4 w1 = *reinterpret_cast<const uint4*>(tb.win + M + n0);
+                    const T* wh = reinterpret_cast<const T*>(&w0);
+                    const T* wt = reinterpret_cast<const T*>(&w1);
+#pragma unroll
+                    for (int e = 0; e < PER; ++e) { o[e] *= wh[e]; tl[e] *= wt[e]; }
                 }
+#pragma unroll
+                for (int e = 0; e < PER; ++e) { o[e] += tail[i * PER + e]; tail[i * PER + e] = tl[e]; }
                 if (f >= b0) {
                     T* d = dst + (long long)f * M + n0;
                     if (vec) *reinterpret_cast<uint4*>(d) = *reinterpret_cast<uint4*>(o);
                     else
                         for (int e = 0; e < PER; ++e) d[e] = o[e];
                 }
-#pragma unroll
-                for (int e = 0; e < PER; ++e) tail[n0 + e] = tl[e];
             }
             __syncwarp();
         }
