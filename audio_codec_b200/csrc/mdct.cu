@@ -140,7 +140,8 @@ static int launch_fwd_stream(pac_ctx* ctx, const void* x, long long rowStride, i
     const long long units = (long long)nRows * segs;
     const int grid = (int)std::min<long long>(148, (units + W - 1) / W);
     const int vec = aligned16(x) && aligned16(coefs) && (rowStride * sizeof(T)) % 16 == 0;
-    auto kern = k_mdct_fwd_stream<T>;
+    const bool sym = window == PAC_WIN_SINE || window == PAC_WIN_KAISER || window == PAC_WIN_NONE;
+    auto kern = sym ? k_mdct_fwd_stream<T, true> : k_mdct_fwd_stream<T, false>;
     const size_t smem = ms_smem_bytes<T>();
     PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<grid, W * 32, smem, st>>>((const T*)x, rowStride, nFrames, seg, segs, units, win,

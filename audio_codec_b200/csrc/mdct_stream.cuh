@@ -17,9 +17,10 @@
 #pragma once
 #include "mdct.cuh"
 
-#define MS_SKEW(p) ((p) + ((p) >> 5))            // exchange tile: p = 16 l + r (write) and l + 32 r (read) conflict-free
+#define MS_SKEW(p) ((p) + ((p) >> 4))            // exchange tile of complex values: p = 16 l + r (write) and l + 32 r (read)
+                                                 // are conflict-free per half warp (8-byte accesses: 16 lanes per wavefront)
 #define MS_OSK(k) ((k) + (((k) >> 8) << 4))      // staging arrays: k = (l & 15) + 16 r + 256 (l >> 4) conflict-free
-#define MS_TILE 528                              // 512 + skew
+#define MS_TILE 544                              // values per half of the tile: 512 + skew (complex view: 544 entries)
 
 template <typename T> struct MsCfg;
 template <> struct MsCfg<float> { static constexpr int WARPS = 16; };
@@ -58,11 +59,21 @@ template <> struct MsRun<float> {
         o[0] = v.x; o[1] = v.y;
     }
     static __device__ __forceinline__ void st(float* p, const float* o) { *reinterpret_cast<float2*>(p) = make_float2(o[0], o[1]); }
+    static __device__ __forceinline__ cplx<float> ldc(const cplx<float>* p) {
+        float2 v = *reinterpret_cast<const float2*>(p);
+        return {v.x, v.y};
+    }
+    static __device__ __forceinline__ void stc(cplx<float>* p, cplx<float> c) { *reinterpret_cast<float2*>(p) = make_float2(c.x, c.y); }
 };
 template <> struct MsRun<double> {
     static constexpr int L = 1;
     static __device__ __forceinline__ void ld(const double* p, double* o) { o[0] = *p; }
     static __device__ __forceinline__ void st(double* p, const double* o) { *p = o[0]; }
+    static __device__ __forceinline__ cplx<double> ldc(const cplx<double>* p) {
+        double2 v = *reinterpret_cast<const double2*>(p);
+        return {v.x, v.y};
+    }
+    static __device__ __forceinline__ void stc(cplx<double>* p, cplx<double> c) { *reinterpret_cast<double2*>(p) = make_double2(c.x, c.y); }
 };
 
 template <typename T> struct MsBlock {        // one 1024-value block in registers, 16 bytes per access
@@ -143,19 +154,14 @@ template <typename T> __host__ __device__ constexpr size_t ms_smem_bytes() {
 // 512-point FFT of z[lane + 32 i] = u[i]; on return u[r] = Z[(lane & 15) + 16 r + 256 (lane >> 4)].
 // The tile is free again when the function returns.
 template <typename T>
-__device__ __forceinline__ void warp_fft512(cplx<T>* u, T* tileRe, T* tileIm, const MsTables<T>& tb, int lane) {
+__device__ __forceinline__ void warp_fft512(cplx<T>* u, T* tileRe, const MsTables<T>& tb, int lane) {
     bfly16(u);
+    cplx<T>* tile = reinterpret_cast<cplx<T>*>(tileRe);     // [MS_TILE] complex = both halves of the tile
 #pragma unroll
-    for (int r = 0; r < 16; ++r) {
-        tileRe[MS_SKEW(16 * lane + r)] = u[r].x;
-        tileIm[MS_SKEW(16 * lane + r)] = u[r].y;
-    }
+    for (int r = 0; r < 16; ++r) MsRun<T>::stc(tile + MS_SKEW(16 * lane + r), u[r]);
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < 16; ++r) {
-        u[r].x = tileRe[MS_SKEW(lane + 32 * r)];
-        u[r].y = tileIm[MS_SKEW(lane + 32 * r)];
-    }
+    for (int r = 0; r < 16; ++r) u[r] = MsRun<T>::ldc(tile + MS_SKEW(lane + 32 * r));
     __syncwarp();
     const int k = lane & 15;
 #pragma unroll
@@ -173,7 +179,7 @@ __device__ __forceinline__ void warp_fft512(cplx<T>* u, T* tileRe, T* tileIm, co
 
 // ---------------------------------------------------------------- forward
 // unit = (row, run of `seg` frames).  out[row][frame][1024].
-template <typename T>
+template <typename T, bool SYM>
 __global__ void __launch_bounds__(MsCfg<T>::WARPS * 32, 1)
 k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int seg, int segsPerRow, long long nUnits,
                   const T* __restrict__ winG, const cplx<T>* __restrict__ twG, const cplx<T>* __restrict__ rootsG,
@@ -214,18 +220,21 @@ k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int
                 cplx<T> t;
                 if (it < 8) {
                     const int a = H - 1 - n, b = H + n;
-                    const T a0 = E1[512 + a] * W1[512 + a], a1 = E1[b] * W1[b];
-                    const T a2 = E0[512 + a] * W0[512 + a], a3 = E0[b] * W0[b];
+                    // symmetric window (sine / KBD): w[i1] = w[i2], w[i3] = w[i0] - two loads instead of four
+                    const T w0 = W1[512 + a], w2 = W0[512 + a];
+                    const T a0 = E1[512 + a] * w0, a1 = E1[b] * (SYM ? w2 : W1[b]);
+                    const T a2 = E0[512 + a] * w2, a3 = E0[b] * (SYM ? w0 : W0[b]);
                     t.x = -a0 - a1; t.y = a2 - a3;
                 } else {
                     const int a = n - H, b = 3 * H - 1 - n;
-                    const T a0 = E0[a] * W0[a], a1 = E0[512 + b] * W0[512 + b];
-                    const T a2 = E1[a] * W1[a], a3 = E1[512 + b] * W1[512 + b];
+                    const T w0 = W0[a], w1 = W0[512 + b];
+                    const T a0 = E0[a] * w0, a1 = E0[512 + b] * w1;
+                    const T a2 = E1[a] * (SYM ? w1 : W1[a]), a3 = E1[512 + b] * (SYM ? w0 : W1[512 + b]);
                     t.x = a0 - a1; t.y = -a2 - a3;
                 }
                 u[it] = cmul(t, tb.tw[n]);
             }
-            warp_fft512<T>(u, tileRe, tileIm, tb, lane);
+            warp_fft512<T>(u, tileRe, tb, lane);
             // post-twiddle into the staging arrays (even / odd output indices)
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
@@ -302,7 +311,7 @@ k_imdct_ola_stream(const T* __restrict__ X, int nFrames, int seg, int segsPerRow
                     const cplx<T> t = {Ei[n], Ei[512 + Q - 1 - n]};      // {X[2n], X[M-1-2n]}
                     u[it] = cmul(t, tb.tw[n]);
                 }
-                warp_fft512<T>(u, Ev, Ov, tb, lane);
+                warp_fft512<T>(u, Ev, tb, lane);
 #pragma unroll
                 for (int r = 0; r < 16; ++r) {
                     const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
