@@ -9,6 +9,7 @@
 
 #define DEC_NT 256
 #define DEC_REC_MAX 4096          // largest channel-block payload accepted (bytes)
+#define DEC_GROUP 32              // lanes per band in the per-band phases (8 / 16 measured slower: divergent groups of a warp serialise)
 #define DEC_MAX_NODES 512         // split-tree nodes per frame (a 128 kb/s long frame has ~150); sized for 3 CTAs per SM
 
 struct DecSmem {
@@ -116,21 +117,23 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
     const int omPos = dev->sbrCutoff;
     if (dev->useVQ) {
-        for (int b = warp; b < nB; b += DEC_NT / 32) {
+        constexpr int G = DEC_GROUP;
+        const int grp = tid / G, glane = tid & (G - 1);
+        for (int b = grp; b < nB; b += DEC_NT / G) {
             const int bb = S.ba[b];
             if (!bb) continue;
             BitR br = {S.rec, S.bandPos[b], recBits};
             int werr = 0;
             const int cap = S.capOff[b + 1] - S.capOff[b];
             const bool env = sbr && bands.omitted[b];       // one envelope value (coder/codec.py:111-132)
-            warp_parse_gain_shape(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], S.wsA, S.wsB,
+            grp_parse_gain_shape<G>(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], S.wsA, S.wsB,
                                   S.capOff[b], cap, S.nodes, &S.misc[7], DEC_MAX_NODES, &S.bd[b], &werr);
-            if (werr && lane == 0) atomicOr(err, werr);
+            if (werr && glane == 0) atomicOr(err, werr);
         }
         __syncthreads();
         cta_decode_leaves(pt, S.nodes, min(S.misc[7], DEC_MAX_NODES), S.wsA, S.wsB, tid, DEC_NT, err);
         __syncthreads();
-        for (int b = warp; b < nB; b += DEC_NT / 32) {
+        for (int b = grp; b < nB; b += DEC_NT / G) {
             if (!S.ba[b]) continue;
             double* out = S.lines + bands.lower[b];
             if (sbr && bands.omitted[b]) {                  // stored at consecutive lines from the cut-off
@@ -138,7 +141,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
                 for (int q = 0; q < b; ++q) k += bands.omitted[q] ? 1 : 0;
                 out = S.lines + omPos + k;
             }
-            warp_finish_gain_shape(S.nodes, S.bd[b], S.wsA, S.wsB, S.capOff[b], out);
+            grp_finish_gain_shape<G>(S.nodes, S.bd[b], S.wsA, S.wsB, S.capOff[b], out);
         }
     } else {
         for (int b = warp; b < nB; b += DEC_NT / 32) {

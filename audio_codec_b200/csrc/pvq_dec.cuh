@@ -164,22 +164,38 @@ struct BandDec {               // per band, written by phase A (lane 0), read by
 
 struct ParseNode { short off, cap, n, buf; int bits; short root; };
 
+// Sub-warp groups of G lanes (G = 8, 16 or 32): the per-band phases are latency bound (serial tree
+// walks, dependent fp64 transcendentals), so several bands per warp in flight beat one band
+// spread over 32 mostly idle lanes.
+template <int G> __device__ __forceinline__ unsigned grp_mask() {
+    return G == 32 ? 0xffffffffu : (((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1)));
+}
+template <int G> __device__ __forceinline__ double grp_sum(double v, unsigned gmask) {
+#pragma unroll
+    for (int o = G / 2; o; o >>= 1) v += __shfl_xor_sync(gmask, v, o);
+    return v;
+}
+
+template <int G>
 __device__ __forceinline__ int dn_append(DNode* nodes, int* nNodes, int maxNodes, const DNode& nd, int* err) {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & (G - 1);
+    const unsigned gmask = grp_mask<G>();
     int slot = 0;
     if (lane == 0) slot = atomicAdd(nNodes, 1);
-    slot = __shfl_sync(0xffffffffu, slot, 0);
+    slot = __shfl_sync(gmask, slot, 0, G);
     if (slot >= maxNodes) { *err |= PVQ_ERR_STACK; return -1; }
     if (lane == 0) nodes[slot] = nd;
     return slot;
 }
 
-// Phase A for one band on one warp.  base = offset of the band's region (capacity cap, a power of
+// Phase A for one band on one group of G lanes (G = 8: four bands per warp in flight).  base = offset of the band's region (capacity cap, a power of
 // two >= L) in the workspaces.  All lanes hold the same cursor and run the scalar logic redundantly.
-__device__ __forceinline__ void warp_parse_gain_shape(const PvqTab& t, BitR& br, int R, int L, double* wsA, double* wsB,
+template <int G>
+__device__ __forceinline__ void grp_parse_gain_shape(const PvqTab& t, BitR& br, int R, int L, double* wsA, double* wsB,
                                                       int base, int cap, DNode* nodes, int* nNodes, int maxNodes,
                                                       BandDec* bd, int* err) {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & (G - 1);
+    const unsigned gmask = grp_mask<G>();
     int bg, bs, tail = -1;
     gs_alloc(t, R, L, &bg, &bs);
     if (bs != 0) {
@@ -200,7 +216,7 @@ __device__ __forceinline__ void warp_parse_gain_shape(const PvqTab& t, BitR& br,
                 dn.K = (int)K;
                 dn.flags |= DN_LEAF;
                 used += w;
-                tail = dn_append(nodes, nNodes, maxNodes, dn, err);
+                tail = dn_append<G>(nodes, nNodes, maxNodes, dn, err);
                 if (tail < 0) break;
                 continue;
             }
@@ -213,13 +229,13 @@ __device__ __forceinline__ void warp_parse_gain_shape(const PvqTab& t, BitR& br,
             const double theta = dequantize_uniform(ti, aT) * 1.5707963267948966;
             ms_alloc(aMs, theta, half, &aMid, &aSide);
             double* oth = (nd.buf ? wsA : wsB) + nd.off;
-            for (int i = lane; i < half; i += 32) {       // children that get no bits stay zero
+            for (int i = lane; i < half; i += G) {       // children that get no bits stay zero
                 if (aMid <= 0) oth[i] = 0.0;
                 if (aSide <= 0) oth[hc + i] = 0.0;
             }
             dn.u = (unsigned long long)__double_as_longlong(theta);
             dn.K = 0;
-            tail = dn_append(nodes, nNodes, maxNodes, dn, err);
+            tail = dn_append<G>(nodes, nNodes, maxNodes, dn, err);
             if (tail < 0) break;
             if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
             if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, 0};
@@ -252,13 +268,15 @@ __device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, const DNode* 
     }
 }
 
-// Phase C for one band on one warp: out[0..L) <- gain * shape.  base as in phase A.
-__device__ __forceinline__ void warp_finish_gain_shape(const DNode* nodes, const BandDec& bd, double* wsA, double* wsB,
+// Phase C for one band on one group of G lanes: out[0..L) <- gain * shape.  base as in phase A.
+template <int G>
+__device__ __forceinline__ void grp_finish_gain_shape(const DNode* nodes, const BandDec& bd, double* wsA, double* wsB,
                                                        int base, double* out) {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & (G - 1);
+    const unsigned gmask = grp_mask<G>();
     const int L = bd.L;
     if (bd.tail < 0) {
-        for (int i = lane; i < L; i += 32) out[i] = bd.gain;                 // shape = ones
+        for (int i = lane; i < L; i += G) out[i] = bd.gain;                 // shape = ones
         return;
     }
     for (int idx = bd.tail; idx >= 0;) {
@@ -271,11 +289,11 @@ __device__ __forceinline__ void warp_finish_gain_shape(const DNode* nodes, const
             const int reps = (nd.flags & DN_ROOT) ? 2 : 1;                   // a root leaf is normalised twice
             for (int r = 0; r < reps; ++r) {
                 double ss = 0.0;
-                for (int i = lane; i < n; i += 32) ss += cur[i] * cur[i];
-                const double nr = sqrt(warp_sum(ss));
+                for (int i = lane; i < n; i += G) ss += cur[i] * cur[i];
+                const double nr = sqrt(grp_sum<G>(ss, gmask));
                 if (nr != 0.0)
-                    for (int i = lane; i < n; i += 32) cur[i] = cur[i] / nr;
-                __syncwarp();
+                    for (int i = lane; i < n; i += G) cur[i] = cur[i] / nr;
+                __syncwarp(gmask);
             }
             continue;
         }
@@ -284,7 +302,7 @@ __device__ __forceinline__ void warp_finish_gain_shape(const DNode* nodes, const
         const double theta = __longlong_as_double((long long)nd.u);
         const double ct = cos(theta), sn = sin(theta), r2 = sqrt(2.0);
         double ss = 0.0;
-        for (int i = lane; i < half; i += 32) {
+        for (int i = lane; i < half; i += G) {
             const double m = oth[i], s = oth[hc + i];
             const double l = (m * ct + s * sn) / r2;
             const double r = (m * ct - s * sn) / r2;
@@ -292,12 +310,12 @@ __device__ __forceinline__ void warp_finish_gain_shape(const DNode* nodes, const
             cur[mid + i] = r;
             ss += r * r;
         }
-        const double nr = sqrt(warp_sum(ss));
-        __syncwarp();
+        const double nr = sqrt(grp_sum<G>(ss, gmask));
+        __syncwarp(gmask);
         if (nr != 0.0)
-            for (int i = lane; i < n; i += 32) cur[i] = cur[i] / nr;
-        __syncwarp();
+            for (int i = lane; i < n; i += G) cur[i] = cur[i] / nr;
+        __syncwarp(gmask);
     }
-    for (int i = lane; i < L; i += 32) out[i] = bd.gain * wsA[base + i];
-    __syncwarp();
+    for (int i = lane; i < L; i += G) out[i] = bd.gain * wsA[base + i];
+    __syncwarp(gmask);
 }

@@ -1,0 +1,119 @@
+"""GPU parity on the edge cases of the stream API: ragged batches, tiny inputs, silence, clipping,
+mono, transients with SBR, block floating point - each byte-identical to the oracle's .pac and
+bit-identical in decoded PCM - plus size-independent properties at a larger batch."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.dirname(__file__))
+
+pytestmark = pytest.mark.gpu
+
+
+from edge_signals import sig as _sig, cases as _cases  # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "edge.npz")
+# Pure DC through the sine window is analytically ONE MDCT line; every other line is the FFT's own
+# rounding noise (~1e-18), which the reference nevertheless quantises (bands 1-14 get bits).  Its code
+# words there change under a 1-ulp perturbation of the input (tools/ and DESIGN.md, "ill-conditioned
+# inputs"), so no implementation with a different FFT summation order can reproduce them: for this
+# case the stream must be valid and decode to the same audio instead.  (The on/off steps around the DC
+# run are as structured: exactly tied PVQ residuals, resolved by np.argmax on rounding noise.)
+ILL_CONDITIONED = {"dc"}
+
+
+def _check(pcm_list, fs, rate, use_vq=True, use_sbr=None):
+    from audio_codec_b200 import _lib, engine
+    from oracle import pac as opac
+    C = pcm_list[0].shape[0]
+    ctx = _lib.Context(sample_rate=fs, n_channels=C, rate_kbps=rate, use_vq=use_vq, use_sbr=use_sbr)
+    got = engine.encode_streams(ctx, pcm_list)
+    dec = engine.decode_streams(got)
+    for i, (pcm, g, y) in enumerate(zip(pcm_list, got, dec)):
+        ref = opac.encode_pcm(pcm, fs, rate, use_vq=use_vq, use_sbr=use_sbr)
+        assert g == ref, f"stream {i} (n={pcm.shape[1]}): .pac differs from the oracle ({len(g)} vs {len(ref)} bytes)"
+        _, yr = opac.decode_pac(ref)
+        assert y.shape == yr.shape, (i, y.shape, yr.shape)
+        assert np.array_equal(y, yr), f"stream {i}: PCM max diff {np.abs(y.astype(int) - yr.astype(int)).max()}"
+
+
+def test_ragged_batch_of_tiny_streams():
+    _check([_sig(n, 48000, 10 + n) for n in (1, 1023, 1024, 1025, 3000)], 48000, 128)
+
+
+@pytest.mark.parametrize("rate", [128, 96])
+def test_reference_goldens_edge_cases(rate):
+    """Every edge signal, encoded in ONE ragged batch per channel count, against the .pac bytes and the
+    PCM the unmodified reference produced (tests/golden/make_edge_golden.py)."""
+    from audio_codec_b200 import _lib, engine
+    from oracle import pac as opac
+    g = np.load(GOLD)
+    cases = _cases()
+    for nch, fs in ((2, 48000), (1, 44100)):
+        names = [n for n, (f, x) in cases.items() if x.shape[0] == nch and f == fs]
+        ctx = _lib.Context(sample_rate=fs, n_channels=nch, rate_kbps=rate)
+        got = engine.encode_streams(ctx, [cases[n][1] for n in names])
+        dec = engine.decode_streams(got)
+        for n, buf, y in zip(names, got, dec):
+            ref = g[f"{n}_{rate}_pac"].tobytes()
+            ypcm = g[f"{n}_{rate}_pcm"]
+            if n in ILL_CONDITIONED:
+                assert len(buf) == len(ref) and buf[:30] == ref[:30]
+                _, yo = opac.decode_pac(buf)                      # the reference-exact decoder accepts the stream
+                assert np.array_equal(yo, y)
+                m = ypcm.shape[1]
+                # a tied pulse resolved the other way moves one PVQ pulse: tens of LSB at most, same noise level
+                assert np.abs(y[:, :m].astype(int) - ypcm.astype(int)).max() <= 64, n
+                continue
+            assert buf == ref, f"{n}@{rate}: .pac differs from the reference"
+            m = ypcm.shape[1]                                     # the reference trims its output file
+            assert y.shape[1] >= m and np.array_equal(y[:, :m], ypcm), f"{n}@{rate}: PCM differs"
+
+
+def test_mono_44k():
+    _check([_sig(5000, 44100, 5, C=1), _sig(2048, 44100, 6, C=1)], 44100, 128)
+
+
+def test_transients_with_sbr_96k():
+    n = 9000
+    x = _sig(n, 48000, 7)
+    x[:, ::1500] = 30000
+    x[:, 1::1500] = -30000
+    _check([x, _sig(4000, 48000, 8)], 48000, 96)
+
+
+def test_block_floating_point_ragged():
+    x = _sig(6000, 48000, 9)
+    x[:, 2500] = 32000
+    _check([x, _sig(1500, 48000, 11), np.zeros((2, 2048), np.int16)], 48000, 128, use_vq=False)
+
+
+def test_batch_invariance_determinism_and_lengths():
+    """Size-independent properties on 48 streams x 1.5 s: a stream's bytes do not depend on its batch,
+    two runs agree, stream sizes follow the reference's numSamples rule, decode is shape-exact."""
+    from audio_codec_b200 import _lib, engine
+    fs = 48000
+    lens = [int(fs * 1.5) - 97 * i for i in range(48)]
+    pcm = [_sig(n, fs, 100 + i) for i, n in enumerate(lens)]
+    ctx = _lib.Context(sample_rate=fs, n_channels=2, rate_kbps=128)
+    a = engine.encode_streams(ctx, pcm)
+    b = engine.encode_streams(ctx, pcm)
+    assert a == b
+    for i in (0, 7, 47):
+        assert engine.encode_streams(ctx, [pcm[i]])[0] == a[i]
+    rev = engine.encode_streams(ctx, pcm[::-1])[::-1]
+    assert rev == a
+    dec = engine.decode_streams(a)
+    for n, buf, y in zip(lens, a, dec):
+        h = engine.parse_header(buf)
+        nb = -(-n // 1024)
+        nrec = len(engine.block_records(buf))
+        # blocks 0..nb-1, the last one again, Close()'s flush - minus transient blocks the reference drops
+        # (all-zero sub-frame, coder/pacfile.py:421-447), which can only be the zero-padded tail here
+        assert nrec in (2 * (nb + 2), 2 * (nb + 1))
+        assert y.shape == (2, (nrec // 2 + 1) * 1024)                # every coded block + the overlap flush
+        # lossy but close: the decoder output is the input delayed by one block
+        err = y[:, 1024:1024 + n].astype(np.float64) - pcm[lens.index(n)].astype(np.float64)
+        assert np.sqrt(np.mean(err ** 2)) < 0.25 * np.sqrt(np.mean(pcm[lens.index(n)].astype(np.float64) ** 2))

@@ -162,3 +162,20 @@ def test_full_files_identical_to_shipped_fixtures(name, rate):
     fs, pcm, nh = pac.read_wav_like_reference(os.path.join(REF, "test_signals", f"{name}.wav"))
     out = pac.encode_pcm(pcm, fs, rate, header_samples=nh)
     assert hashlib.md5(out).hexdigest() == md5[f"{name}_coded_{rate}.pac"]
+
+
+@pytest.mark.parametrize("rate", [128, 96])
+def test_edge_cases_identical_to_reference(rate):
+    """Silence, DC, clipping square wave, 1 / 1023 / 1025-sample inputs, transients, mono: the oracle's
+    .pac bytes and decoded PCM against the unmodified reference (tests/golden/make_edge_golden.py)."""
+    import sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    import edge_signals
+    from oracle import pac as opac
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "edge.npz"))
+    for name, (fs, pcm) in edge_signals.cases().items():
+        ref = g[f"{name}_{rate}_pac"].tobytes()
+        assert opac.encode_pcm(pcm, fs, rate) == ref, name
+        _, y = opac.decode_pac(ref)
+        want = g[f"{name}_{rate}_pcm"]
+        assert np.array_equal(y[:, :want.shape[1]], want), name
