@@ -211,14 +211,17 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
             }
         }
         PHASE(4);
-        // levels: the nodes of one tree depth of all bands, spread over all warps
+        // levels: the nodes of one tree depth of all bands - vector work on one warp per node,
+        // then the scalar planning of every node of the level in parallel threads
+        double* sideNorm = S.mk;                            // [ENC_MAX_NODES]; S.mk is free until the leaves step
         __syncthreads();
         for (int lvl0 = 0, lvl1 = min(S.misc[6], ENC_MAX_NODES); lvl0 < lvl1;) {
-            __syncthreads();                                // everyone has read the level bounds
-            for (int i = lvl0 + warp; i < lvl1; i += ENC_NT / 32) {
+            for (int i = lvl0 + warp; i < lvl1; i += ENC_NT / 32) warp_split_node(S.nodes, i, sideNorm, wsA, wsB);
+            __syncthreads();
+            for (int i = lvl0 + tid; i < lvl1; i += ENC_NT) {
                 int werr = 0;
-                warp_plan_node(pt, S.nodes, i, &S.misc[6], ENC_MAX_NODES, wsA, wsB, &werr);
-                if (werr && lane == 0) atomicOr(err, werr);
+                thread_plan_node(pt, S.nodes, i, sideNorm, &S.misc[6], ENC_MAX_NODES, &werr);
+                if (werr) atomicOr(err, werr);
             }
             __syncthreads();
             lvl0 = lvl1;

@@ -353,18 +353,12 @@ __device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& 
     return acc;
 }
 
-// One tree node on one warp (levels step).  count: pool fill; the node's children are appended.
-__device__ __forceinline__ void warp_plan_node(const PvqTab& t, TNode* nodes, int i, int* count, int maxNodes,
-                                               double* wsA, double* wsB, int* err) {
+// Levels step, part 1 - one tree node on one warp: the vector work of an internal node (mid/side
+// split, norms, normalised halves).  The two norms go to nodes[i].val (mid) and side[i] for part 2.
+__device__ __forceinline__ void warp_split_node(TNode* nodes, int i, double* side, double* wsA, double* wsB) {
     const int lane = threadIdx.x & 31;
     const TNode nd = nodes[i];
-    if (nd.bits <= PVQ_SPLIT_BITS) {                      // leaf: pulses and index width from the table
-        long long K;
-        int w;
-        pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
-        if (lane == 0) { nodes[i].K = (int)K; nodes[i].w = (unsigned char)w; }
-        return;
-    }
+    if (nd.bits <= PVQ_SPLIT_BITS) return;                // leaf: nothing to split
     double* cur = (nd.buf ? wsB : wsA) + nd.off;
     double* oth = (nd.buf ? wsA : wsB) + nd.off;
     const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = (1 << nd.capLog2) / 2;
@@ -384,7 +378,30 @@ __device__ __forceinline__ void warp_plan_node(const PvqTab& t, TNode* nodes, in
         if (nm != 0.0) oth[k] = oth[k] / nm;
         if (ns != 0.0) oth[hc + k] = oth[hc + k] / ns;
     }
-    const double theta = nm == 0.0 ? 0.0 : atan(ns / nm);
+    if (lane == 0) {
+        nodes[i].val = (unsigned long long)__double_as_longlong(nm);
+        side[i] = ns;
+    }
+}
+
+// Levels step, part 2 - one tree node on ONE thread: the scalar work (angle, its quantisation, the
+// bit split with its fp64 transcendentals, the children).  All nodes of a level run in parallel
+// lanes, so a level pays the atan / tan / log2 latency chain once instead of once per node.
+// count: pool fill; the node's children are appended.
+__device__ __forceinline__ void thread_plan_node(const PvqTab& t, TNode* nodes, int i, const double* side, int* count,
+                                                 int maxNodes, int* err) {
+    const TNode nd = nodes[i];
+    if (nd.bits <= PVQ_SPLIT_BITS) {                      // leaf: pulses and index width from the table
+        long long K;
+        int w;
+        pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+        nodes[i].K = (int)K;
+        nodes[i].w = (unsigned char)w;
+        return;
+    }
+    const int half = (nd.n + 1) / 2, hc = (1 << nd.capLog2) / 2;
+    const double nm = __longlong_as_double((long long)nd.val), ns = side[i];
+    const double theta = nm == 0.0 ? 0.0 : pm_atan(ns / nm);
     int aT, aMs, aMid, aSide;
     gs_alloc(t, nd.bits, half, &aT, &aMs);
     const double hp = 1.5707963267948966;                // np.pi / 2
@@ -392,26 +409,24 @@ __device__ __forceinline__ void warp_plan_node(const PvqTab& t, TNode* nodes, in
     const unsigned long long ti = quantize_uniform(theta / hp, aT);
     const double tq = dequantize_uniform(ti, aT) * hp;
     ms_alloc(aMs, tq, half, &aMid, &aSide);
-    if (lane == 0) {
-        const int nk = (aMid > 0) + (aSide > 0);
-        int slot = nk ? atomicAdd(count, nk) : 0;
-        short k0 = -1, k1 = -1;
-        if (slot + nk > maxNodes) {
-            *err |= PVQ_ERR_STACK;
-        } else {
-            TNode c;
-            c.val = 0ull; c.K = -2; c.n = (short)half; c.kid[0] = c.kid[1] = -1;
-            c.capLog2 = (unsigned char)(nd.capLog2 - 1); c.buf = (unsigned char)(1 - nd.buf); c.band = nd.band; c.w = 0;
-            c.logSlot = -1; c.pad = 0;
-            if (aMid > 0) { c.off = nd.off; c.bits = aMid; k0 = (short)slot; nodes[slot++] = c; }
-            if (aSide > 0) { c.off = (short)(nd.off + hc); c.bits = aSide; k1 = (short)slot; nodes[slot] = c; }
-        }
-        nodes[i].val = ti;
-        nodes[i].K = -1;
-        nodes[i].w = (unsigned char)aT;
-        nodes[i].kid[0] = k0;
-        nodes[i].kid[1] = k1;
+    const int nk = (aMid > 0) + (aSide > 0);
+    int slot = nk ? atomicAdd(count, nk) : 0;
+    short k0 = -1, k1 = -1;
+    if (slot + nk > maxNodes) {
+        *err |= PVQ_ERR_STACK;
+    } else {
+        TNode c;
+        c.val = 0ull; c.K = -2; c.n = (short)half; c.kid[0] = c.kid[1] = -1;
+        c.capLog2 = (unsigned char)(nd.capLog2 - 1); c.buf = (unsigned char)(1 - nd.buf); c.band = nd.band; c.w = 0;
+        c.logSlot = -1; c.pad = 0;
+        if (aMid > 0) { c.off = nd.off; c.bits = aMid; k0 = (short)slot; nodes[slot++] = c; }
+        if (aSide > 0) { c.off = (short)(nd.off + hc); c.bits = aSide; k1 = (short)slot; nodes[slot] = c; }
     }
+    nodes[i].val = ti;
+    nodes[i].K = -1;
+    nodes[i].w = (unsigned char)aT;
+    nodes[i].kid[0] = k0;
+    nodes[i].kid[1] = k1;
 }
 
 // Layout step for one band on ONE thread: stream order is pre-order [theta, mid.., side..], then

@@ -43,6 +43,13 @@ byfile = collections.Counter()
 for (f, l), v in agg.items():
     byfile[f] += v[0]
 print("by file:", {f: round(c / ts, 3) for f, c in byfile.most_common()})
+byfile_i = collections.Counter()
+for (f, l), v in agg.items():
+    byfile_i[f] += v[1]
+print("inst by file:", {f: round(c / ti, 3) for f, c in byfile_i.most_common()})
+if len(sys.argv) > 4:      # inst-sorted listing
+    for (f, l), v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:int(sys.argv[4])]:
+        print(f"I {f}:{l:<4d} inst {v[1]/ti:6.3f} smp {v[0]/ts:6.3f} {v[2]}")
 for (f, l), v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     st = ",".join(f"{k[6:]}:{c}" for k, c in stall[(f, l)].most_common(3))
     print(f"{f}:{l:<4d} smp {v[0]/ts:6.3f} inst {v[1]/ti:6.3f} [{st}] {v[2]}")
