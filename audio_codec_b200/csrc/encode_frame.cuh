@@ -141,26 +141,31 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
         else budget -= (double)(dev->nScaleBits * (nB + 1));
         budget -= (double)(dev->nMantSizeBits * nB);
         warp_bit_alloc(budget, dev->maxMantBits, nB, S.nlEff, S.smr, S.tmp, S.ba);
+        __syncwarp();
+        // per-band private bit buffer (words) and pow2 workspace offsets: exclusive scans over the bands
+        int w = 0, c = 0;
+        if (lane < nB) {
+            const int bits = S.ba[lane] * S.nlEff[lane];
+            w = (bits + 31) / 32 + 3;                     // slack: a 64-bit put may straddle
+            c = 1;
+            while (c < bands.nLines[lane]) c <<= 1;
+        }
+        int wi = w, ci = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int tw = __shfl_up_sync(0xffffffffu, wi, o), tc = __shfl_up_sync(0xffffffffu, ci, o);
+            if (lane >= o) { wi += tw; ci += tc; }
+        }
+        if (lane < nB) { S.wordOff[lane] = wi - w; S.capOff[lane] = ci - c; }
+        if (lane == nB - 1) {
+            S.wordOff[nB] = wi;
+            S.capOff[nB] = ci;
+            if (wi > BAND_WORDS || ci > (isLong ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
+        }
     }
-    __syncthreads();
 
     PHASE(3);
     // (5) quantise each coded band into its private bit buffer
-    if (tid == 0) {
-        int w = 0, c = 0;
-        for (int b = 0; b < nB; ++b) {
-            S.wordOff[b] = w;
-            S.capOff[b] = c;
-            int bits = S.ba[b] * S.nlEff[b];
-            w += (bits + 31) / 32 + 3;                    // slack: a 64-bit put may straddle
-            int cap = 1;
-            while (cap < bands.nLines[b]) cap <<= 1;
-            c += cap;
-        }
-        S.wordOff[nB] = w;
-        S.capOff[nB] = c;
-        if (w > BAND_WORDS || c > (isLong ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
-    }
     for (int i = tid; i < BAND_WORDS; i += ENC_NT) S.bandbits[i] = 0u;
     __syncthreads();
     if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (isLong ? 2048 : 256)) return 0;

@@ -149,8 +149,11 @@ __device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR
 //            normalise leaves, recombine mid/side, then apply the gain
 // Offsets in DNode are absolute positions in the CTA's ping-pong workspaces wsA / wsB.
 struct DNode {
-    unsigned long long u;      // leaf: Fischer index; internal: theta (double bits)
-    int K;                     // leaf: pulses
+    unsigned long long u;      // leaf: Fischer index; internal: theta, then cos(theta) after phase B (double bits)
+    union {
+        int K;                 // leaf: pulses
+        double sn;             // internal: sin(theta), written by phase B
+    };
     short off, n, prev;        // workspace offset, length, previous node of the same band (-1: none)
     unsigned char capLog2, flags;
 };
@@ -256,12 +259,18 @@ __device__ __forceinline__ void grp_parse_gain_shape(const PvqTab& t, BitR& br, 
 }
 
 // Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...
-__device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, const DNode* nodes, int nNodes, double* wsA,
+__device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, DNode* nodes, int nNodes, double* wsA,
                                                   double* wsB, int tid, int nThreads, int* err) {
     const int nWarps = nThreads >> 5;                      // node j -> warp j % nWarps, lane j / nWarps
     for (int i = (tid & 31) * nWarps + (tid >> 5); i < nNodes; i += nThreads) {
         const DNode nd = nodes[i];
-        if (!(nd.flags & DN_LEAF)) continue;
+        if (!(nd.flags & DN_LEAF)) {                       // rotation of the recombine step, once per node
+            double sn, ct;
+            pm_sincos(__longlong_as_double((long long)nd.u), &sn, &ct);
+            nodes[i].u = (unsigned long long)__double_as_longlong(ct);
+            nodes[i].sn = sn;
+            continue;
+        }
         int werr = 0;
         pvq_vector(t, nd.u, nd.n, nd.K, ((nd.flags & DN_BUF) ? wsB : wsA) + nd.off, &werr);
         if (werr) atomicOr(err, werr);
@@ -299,8 +308,7 @@ __device__ __forceinline__ void grp_finish_gain_shape(const DNode* nodes, const 
         }
         // recombine (coder/gain_shape_quantize.py:449-463)
         const int mid = n / 2, half = (n + 1) / 2, hc = (1 << nd.capLog2) / 2;
-        const double theta = __longlong_as_double((long long)nd.u);
-        const double ct = cos(theta), sn = sin(theta), r2 = sqrt(2.0);
+        const double ct = __longlong_as_double((long long)nd.u), sn = nd.sn, r2 = sqrt(2.0);
         double ss = 0.0;
         for (int i = lane; i < half; i += G) {
             const double m = oth[i], s = oth[hc + i];
