@@ -69,7 +69,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     const int nB = bands.nBands;
     // (1) frame header: overall scale, bit allocations (+ BFP scale factors): thread 0
     if (tid == 0) {
-        BitR br = {S.rec, S.misc[3], recBits};
+        BitR br = {S.rec, S.misc[3], recBits, DEC_REC_MAX};
         S.misc[7] = 0;
         S.misc[5] = (int)br_get(br, dev->nScaleBits);
         bool anyOm = false;
@@ -122,7 +122,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
         for (int b = grp; b < nB; b += DEC_NT / G) {
             const int bb = S.ba[b];
             if (!bb) continue;
-            BitR br = {S.rec, S.bandPos[b], recBits};
+            BitR br = {S.rec, S.bandPos[b], recBits, DEC_REC_MAX};
             int werr = 0;
             const int cap = S.capOff[b + 1] - S.capOff[b];
             const bool env = sbr && bands.omitted[b];       // one envelope value (coder/codec.py:111-132)
@@ -149,7 +149,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
             if (!bb) continue;
             const int lo = bands.lower[b], n = bands.nLines[b];
             for (int i = lane; i < n; i += 32) {
-                BitR br = {S.rec, (long long)S.bandPos[b] + (long long)i * bb, recBits};
+                BitR br = {S.rec, (long long)S.bandPos[b] + (long long)i * bb, recBits, DEC_REC_MAX};
                 unsigned m = (unsigned)br_get(br, bb);
                 S.lines[lo + i] = dequantize_bfp(S.sfb[b], m, dev->nScaleBits, bb);
             }

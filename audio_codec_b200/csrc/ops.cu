@@ -390,7 +390,7 @@ k_gs_dequantize(const PacDev* __restrict__ dev, const unsigned char* __restrict_
     const long long v = blockIdx.x;
     const int lane = threadIdx.x;
     PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
-    BitR br = {bytes, bitpos[v], nBits};
+    BitR br = {bytes, bitpos[v], nBits, 0};
     int werr = 0;
     warp_dequantize_gain_shape(pt, br, budget[v], L, wsA, wsB, cap, res, &werr);
     for (int i = lane; i < L; i += 32) out[v * L + i] = res[i];
@@ -512,7 +512,7 @@ k_unpack_bits(const unsigned char* __restrict__ in, int rowBytes, const long lon
             if (lane >= o) inc += t;
         }
         if (f < nf) {
-            BitR br = {in + row * rowBytes, base + inc - wd, 8LL * rowBytes};
+            BitR br = {in + row * rowBytes, base + inc - wd, 8LL * rowBytes, 0};
             val[row * maxF + f] = br_get(br, wd);
         }
         base += __shfl_sync(0xffffffffu, inc, 31);
