@@ -118,17 +118,20 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     const int omPos = dev->sbrCutoff;
     if (dev->useVQ) {
         constexpr int G = DEC_GROUP;
-        const int grp = tid / G, glane = tid & (G - 1);
-        for (int b = grp; b < nB; b += DEC_NT / G) {
-            const int bb = S.ba[b];
-            if (!bb) continue;
+        const int grp = tid / G;
+        // phase A is scalar: one THREAD per band, bands dealt round-robin to the warps (<= 4 per warp)
+        {
+            const int b = lane * (DEC_NT / 32) + warp;
+            const int bb = b < nB ? S.ba[b] : 0;
+            if (bb) {
             BitR br = {S.rec, S.bandPos[b], recBits, DEC_REC_MAX};
             int werr = 0;
             const int cap = S.capOff[b + 1] - S.capOff[b];
             const bool env = sbr && bands.omitted[b];       // one envelope value (coder/codec.py:111-132)
-            grp_parse_gain_shape<G>(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], S.wsA, S.wsB,
-                                  S.capOff[b], cap, S.nodes, &S.misc[7], DEC_MAX_NODES, &S.bd[b], &werr);
-            if (werr && glane == 0) atomicOr(err, werr);
+            grp_parse_gain_shape<1>(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], S.wsA, S.wsB,
+                                    S.capOff[b], cap, S.nodes, &S.misc[7], DEC_MAX_NODES, &S.bd[b], &werr);
+            if (werr) atomicOr(err, werr);
+            }
         }
         __syncthreads();
         cta_decode_leaves(pt, S.nodes, min(S.misc[7], DEC_MAX_NODES), S.wsA, S.wsB, tid, DEC_NT, err);
