@@ -393,6 +393,8 @@ extern "C" void pac_destroy(pac_ctx* c) {
     if (c->pinned) cudaFreeHost(c->pinned);
     for (int i = 0; i < 2; ++i) if (c->io[i]) cudaFree(c->io[i]);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(c->ev[i]);
+    if (c->cpReady)
+        for (int i = 0; i < 2; ++i) { cudaStreamDestroy(c->cp[i]); cudaEventDestroy(c->cpEv[i]); }
     delete c;
 }
 

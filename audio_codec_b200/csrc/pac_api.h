@@ -17,6 +17,9 @@ struct pac_ctx {
     size_t pinnedBytes;
     void* io[2];         // device staging for the host-buffer entry points
     size_t ioBytes[2];
+    cudaStream_t cp[2];  // copy streams of the host-buffer entry points (created on first use)
+    cudaEvent_t cpEv[2];
+    int cpReady;
     cudaEvent_t ev[4];   // around k_encode and k_decode, for pac_last_kernel_ms
     int evValid[2];
     // windows of arbitrary length for pac_window, built on demand

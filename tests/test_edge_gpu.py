@@ -117,3 +117,37 @@ def test_batch_invariance_determinism_and_lengths():
         # lossy but close: the decoder output is the input delayed by one block
         err = y[:, 1024:1024 + n].astype(np.float64) - pcm[lens.index(n)].astype(np.float64)
         assert np.sqrt(np.mean(err ** 2)) < 0.25 * np.sqrt(np.mean(pcm[lens.index(n)].astype(np.float64) ** 2))
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_host_buffer_api_chunked_pipeline_matches_device_path(pinned, monkeypatch):
+    """pac_encode_host / pac_decode_host (host buffers, chunked copy/compute pipeline) against the
+    device-resident entry points on a ragged batch; chunk size forced small so several chunks form."""
+    import torch
+    from audio_codec_b200 import _lib, engine
+    monkeypatch.setenv("PAC_HOST_CHUNK_MB", "0.05")
+    fs = 48000
+    lens = [9000, 2500, 14000, 1024, 7000, 30000, 4097, 11000, 600]
+    pcm = [_sig(n, fs, 300 + i) for i, n in enumerate(lens)]
+    ctx = _lib.Context(sample_rate=fs, n_channels=2, rate_kbps=128)
+    want = engine.encode_streams(ctx, pcm)
+    buf, nbs = engine.pack_pcm(pcm, 2)
+    h_pcm = torch.from_numpy(buf)
+    h_out = torch.empty(sum(len(b) for b in want) + 4096, dtype=torch.uint8)
+    if pinned:
+        h_pcm, h_out = h_pcm.pin_memory(), h_out.pin_memory()
+    off, err = engine.encode_host(ctx, h_pcm, nbs, lens, h_out)
+    assert err == 0
+    out = h_out.numpy().tobytes()
+    got = [out[int(off[s]):int(off[s + 1])] for s in range(len(pcm))]
+    assert got == want
+    ref = engine.decode_streams(want)
+    n_pcm = sum(y.size for y in ref)
+    h_dec = torch.empty(n_pcm, dtype=torch.int16)
+    if pinned:
+        h_dec = h_dec.pin_memory()
+    po, err = engine.decode_host(ctx, h_out, off, h_dec)
+    assert err == 0 and int(po[-1]) == n_pcm
+    y = h_dec.numpy()
+    for s, r in enumerate(ref):
+        assert np.array_equal(y[int(po[s]):int(po[s + 1])].reshape(2, -1), r), s
