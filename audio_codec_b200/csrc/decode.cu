@@ -252,3 +252,13 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
     if (h_err) *h_err = err;
     return err ? PAC_ERR_SOFT : 0;
 }
+
+#ifdef PAC_PHASE_TIMING
+// debug: copy and reset the decoder's per-phase cycle counters ([0..15] long frames, [16..31] short sub-frames)
+extern "C" int pac_debug_phases_dec(unsigned long long* h_out) {
+    unsigned long long z[32] = {0};
+    cudaMemcpyFromSymbol(h_out, g_pac_dphase, sizeof(z));
+    cudaMemcpyToSymbol(g_pac_dphase, z, sizeof(z));
+    return 0;
+}
+#endif

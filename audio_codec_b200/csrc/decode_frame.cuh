@@ -7,6 +7,15 @@
 #include "psy.cuh"
 #include "pvq_dec.cuh"
 
+// Optional per-phase cycle accounting of the decoder (-DPAC_PHASE_TIMING; pac_debug_phases_dec).
+#ifdef PAC_PHASE_TIMING
+static __device__ unsigned long long g_pac_dphase[32];
+#define DPHASE_T0(isLong) long long dph_t_ = clock64(); const int dph_off_ = (isLong) ? 0 : 16
+#define DPHASE(i) do { __syncthreads(); if (threadIdx.x == 0) { long long n_ = clock64(); atomicAdd(&g_pac_dphase[(i) + dph_off_], (unsigned long long)(n_ - dph_t_)); dph_t_ = n_; } } while (0)
+#else
+#define DPHASE_T0(isLong)
+#define DPHASE(i)
+#endif
 #define DEC_NT 256
 #define DEC_REC_MAX 4096          // largest channel-block payload accepted (bytes)
 #define DEC_GROUP 32              // lanes per band in the per-band phases (8 / 16 measured slower: divergent groups of a warp serialise)
@@ -67,6 +76,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const PacBands& bands = isLong ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
+    DPHASE_T0(isLong);
     // (1) frame header: overall scale, bit allocations (+ BFP scale factors): thread 0
     if (tid == 0) {
         BitR br = {S.rec, S.misc[3], recBits, DEC_REC_MAX};
@@ -112,9 +122,10 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     __syncthreads();
     const bool sbr = S.misc[6] != 0;
     const int scale = S.misc[5];
+    DPHASE(0);
     // (2) bands: VQ in three phases (parse per band / index decode per leaf / recombine per band),
     //     block floating point directly
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
     const int omPos = dev->sbrCutoff;
     if (dev->useVQ) {
         constexpr int G = DEC_GROUP;
@@ -133,8 +144,10 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
             if (werr) atomicOr(err, werr);
             }
         }
+        DPHASE(1);
         __syncthreads();
         cta_decode_leaves(pt, S.nodes, min(S.misc[7], DEC_MAX_NODES), S.wsA, S.wsB, tid, DEC_NT, err);
+        DPHASE(2);
         __syncthreads();
         for (int b = grp; b < nB; b += DEC_NT / G) {
             if (!S.ba[b]) continue;
@@ -144,7 +157,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
                 for (int q = 0; q < b; ++q) k += bands.omitted[q] ? 1 : 0;
                 out = S.lines + omPos + k;
             }
-            grp_finish_gain_shape<G>(S.nodes, S.bd[b], S.wsA, S.wsB, S.capOff[b], out);
+            grp_finish_gain_shape<G>(dev->thetaTab, S.nodes, S.bd[b], S.wsA, S.wsB, S.capOff[b], out);
         }
     } else {
         for (int b = warp; b < nB; b += DEC_NT / 32) {
@@ -159,6 +172,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
         }
     }
     __syncthreads();
+    DPHASE(3);
     // (3) SBR: envelope smoothing, 2:1 transposition of the low band, per-band envelope
     //     scaling (coder/codec.py:134-194)
     if (isLong && sbr) {
@@ -199,6 +213,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
         }
         __syncthreads();
     }
+    DPHASE(4);
     return scale;
 }
 

@@ -14,8 +14,8 @@
 // Optional per-phase cycle accounting (build with -DPAC_PHASE_TIMING; read with pac_debug_phases).
 #ifdef PAC_PHASE_TIMING
 static __device__ unsigned long long g_pac_phase[32];
-#define PHASE_T0() long long ph_t_ = clock64()
-#define PHASE(i) do { __syncthreads(); if (threadIdx.x == 0) { long long n_ = clock64(); atomicAdd(&g_pac_phase[(i) + (N == PAC_NLONG ? 0 : 16)], (unsigned long long)(n_ - ph_t_)); ph_t_ = n_; } } while (0)
+#define PHASE_T0() long long ph_t_ = clock64(); const int ph_off_ = PH_IS_LONG ? 0 : 16
+#define PHASE(i) do { __syncthreads(); if (threadIdx.x == 0) { long long n_ = clock64(); atomicAdd(&g_pac_phase[(i) + ph_off_], (unsigned long long)(n_ - ph_t_)); ph_t_ = n_; } } while (0)
 #else
 #define PHASE_T0()
 #define PHASE(i)
@@ -127,6 +127,9 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
     const PacBands& bands = isLong ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
     const double up = (double)(1 << scale);
+#define PH_IS_LONG isLong
+    PHASE_T0();
+#undef PH_IS_LONG
     // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)
     if (tid < nB) S.nlEff[tid] = (sbr && bands.omitted[tid]) ? 1 : bands.nLines[tid];
     __syncthreads();
@@ -169,7 +172,7 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
     for (int i = tid; i < BAND_WORDS; i += ENC_NT) S.bandbits[i] = 0u;
     __syncthreads();
     if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (isLong ? 2048 : 256)) return 0;
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
     int* yws = reinterpret_cast<int*>(S.mk);              // masked threshold is dead from here on
     // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
     // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
@@ -332,7 +335,9 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(S.fb);
     T* mkT = reinterpret_cast<T*>(S.mk);
 
+#define PH_IS_LONG (N == PAC_NLONG)
     PHASE_T0();
+#undef PH_IS_LONG
     // (1) window + MDCT (coder/codec.py:301-305)
     mdct_fold<T, N, 1, ENC_NT>(fx, 0, winTab, nullptr, shape, tw, fbuf, tid);
     __syncthreads();

@@ -337,7 +337,7 @@ k_gs_quantize(const PacDev* __restrict__ dev, const double* __restrict__ x, int 
     for (int i = lane; i < nW; i += 32) bits[i] = 0u;
     if (lane == 0) count[v] = 0;
     __syncwarp();
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, nullptr};
     BitW bw = {bits, 0};
     FieldLog lg = {val + v * maxF, width + v * maxF, count + v, maxF};
     int werr = 0;
@@ -389,7 +389,7 @@ k_gs_dequantize(const PacDev* __restrict__ dev, const unsigned char* __restrict_
     double* res = wsB + cap;
     const long long v = blockIdx.x;
     const int lane = threadIdx.x;
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW};
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, nullptr};
     BitR br = {bytes, bitpos[v], nBits, 0};
     int werr = 0;
     warp_dequantize_gain_shape(pt, br, budget[v], L, wsA, wsB, cap, res, &werr);

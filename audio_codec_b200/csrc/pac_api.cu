@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <vector>
 #include "pac_api.h"
+#include "quant.cuh"
 
 static const double kPi = 3.14159265358979323846;
 
@@ -289,6 +290,32 @@ static int make_pvq(pac_ctx* c) {
     return upload(c, off, &c->host.pvqRowOff);
 }
 
+// ---- quantised-angle table (PacDev::thetaTab)
+__global__ void k_theta_tab(double* tab) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < 2 || e >= (2 << PAC_THETA_BITS)) return;
+    const int aT = 31 - __clz(e);
+    const unsigned long long code = (unsigned long long)(e - (1 << aT));
+    const double theta = dequantize_uniform(code, aT) * 1.5707963267948966;      // * np.pi / 2
+    double sn, ct;
+    pm_sincos(theta, &sn, &ct);
+    tab[4 * e + 0] = theta;
+    tab[4 * e + 1] = pm_log2(pm_tan(fabs(theta)) + PAC_EPS);
+    tab[4 * e + 2] = ct;
+    tab[4 * e + 3] = sn;
+}
+static int make_theta(pac_ctx* c) {
+    void* d = nullptr;
+    const size_t n = (size_t)(2 << PAC_THETA_BITS) * 4;
+    if (cudaMalloc(&d, n * sizeof(double)) != cudaSuccess) return PAC_ERR_ALLOC;
+    c->allocs.push_back(d);
+    if (cudaMemset(d, 0, n * sizeof(double)) != cudaSuccess) return PAC_ERR_ALLOC;
+    k_theta_tab<<<(2 << PAC_THETA_BITS) / 256, 256>>>((double*)d);
+    if (cudaDeviceSynchronize() != cudaSuccess) return PAC_ERR_ALLOC;
+    c->host.thetaTab = (const double*)d;
+    return 0;
+}
+
 // ---- SBR decode: scipy.ndimage.gaussian_filter1d(sigma=200, mode='reflect',
 // truncate=4) response to a unit impulse at each of the first nOm positions of a
 // length-2*nLen signal (coder/codec.py:139-146); only the first nLen outputs used.
@@ -368,6 +395,7 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     if (!rc) rc = make_psy(c, PAC_HALF_SHORT, &h.barkShort, &h.threshShort, &h.fftFreqShort, &h.fftNormShort);
     if (!rc) rc = make_pvq(c);
     if (!rc) rc = make_sbr(c);
+    if (!rc) rc = make_theta(c);
     if (!rc) {
         void* d = nullptr;
         if (cudaMalloc(&d, sizeof(PacDev)) != cudaSuccess) rc = PAC_ERR_ALLOC;

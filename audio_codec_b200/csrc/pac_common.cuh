@@ -16,6 +16,7 @@
 #define PAC_HALF_SHORT 128
 #define PAC_SUBFRAMES 8
 #define PAC_PVQ_LMAX 1024
+#define PAC_THETA_BITS 12
 #define PAC_EPS 2.220446049250313e-16   // np.finfo(float).eps
 
 // window shapes (coder/window.py:14-92, selected by coder/codec.py:30-44)
@@ -71,6 +72,10 @@ struct PacDev {
     const double* log2tab;     // [PAC_PVQ_LMAX+1] log2(L) (entry 0 unused)
     // pvq_compute_k_for_R as a table: [(PAC_PVQ_LMAX+1)][33] of {K, field width} for bits = 0..32
     const int2* pvqKW;
+    // quantised mid/side angle: [(1 << aT) + code][4] = {theta, log2(tan|theta| + eps), cos, sin} for
+    // aT = 1..PAC_THETA_BITS, filled on the device at create time with the same device functions the
+    // direct evaluation uses (bit-identical), so the per-node fp64 tan / log2 / sin / cos become loads
+    const double* thetaTab;
     // SBR decode: response of gaussian_filter1d(sigma=200, reflect) to unit impulses
     const double* sbrGauss;    // [nOmitted][2*(1024-cutoff)] (only first half used)
     int sbrNOmitted;

@@ -17,6 +17,7 @@ struct PvqTab {
     const int* off;
     const double* log2tab;   // log2(L), L <= PAC_PVQ_LMAX
     const int2* KW;          // {K, width}[L][bits], bits 0..32
+    const double* theta;     // PacDev::thetaTab or nullptr (direct evaluation)
 };
 
 // N(l,k): rows 0..3 closed form, others from the table; entries past a row's end
@@ -54,6 +55,35 @@ __device__ __forceinline__ void ms_alloc(int aMs, double theta, int len, int* aM
     long long m = 0;
     if (theta != 0.0) {
         double v = floor(((double)aMs - (double)(len - 1) * log2(tan(fabs(theta)) + PAC_EPS)) / 2.0);
+        m = v > 1e15 ? (long long)1e15 : (v < -1e15 ? (long long)-1e15 : (long long)v);
+    }
+    if (m < 0) m = 0;
+    if (m > aMs) m = aMs;
+    *aMid = (int)m;
+    *aSide = aMs - (int)m > 0 ? aMs - (int)m : 0;
+}
+
+// The quantised angle of a split node (aT bits, code ti) and log2(tan|theta| + eps), from the
+// table when it covers aT (entry = its index, for the decoder's cos / sin lookup), else evaluated.
+__device__ __forceinline__ void theta_terms(const PvqTab& t, unsigned long long ti, int aT, double* theta, double* l2t,
+                                            int* entry) {
+    if (t.theta && aT >= 1 && aT <= PAC_THETA_BITS) {
+        const int e = (1 << aT) + (int)ti;
+        *theta = t.theta[4 * e];
+        *l2t = t.theta[4 * e + 1];
+        *entry = e;
+    } else {
+        const double th = dequantize_uniform(ti, aT) * 1.5707963267948966;
+        *theta = th;
+        *l2t = th != 0.0 ? pm_log2(pm_tan(fabs(th)) + PAC_EPS) : 0.0;
+        *entry = -1;
+    }
+}
+// bit_allocation_ms with the logarithm already in hand
+__device__ __forceinline__ void ms_alloc_l2t(int aMs, double theta, double l2t, int len, int* aMid, int* aSide) {
+    long long m = 0;
+    if (theta != 0.0) {
+        double v = floor(((double)aMs - (double)(len - 1) * l2t) / 2.0);
         m = v > 1e15 ? (long long)1e15 : (v < -1e15 ? (long long)-1e15 : (long long)v);
     }
     if (m < 0) m = 0;
@@ -407,8 +437,10 @@ __device__ __forceinline__ void thread_plan_node(const PvqTab& t, TNode* nodes, 
     const double hp = 1.5707963267948966;                // np.pi / 2
     if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
     const unsigned long long ti = quantize_uniform(theta / hp, aT);
-    const double tq = dequantize_uniform(ti, aT) * hp;
-    ms_alloc(aMs, tq, half, &aMid, &aSide);
+    double tq, l2t;
+    int entry;
+    theta_terms(t, ti, aT, &tq, &l2t, &entry);
+    ms_alloc_l2t(aMs, tq, l2t, half, &aMid, &aSide);
     const int nk = (aMid > 0) + (aSide > 0);
     int slot = nk ? atomicAdd(count, nk) : 0;
     short k0 = -1, k1 = -1;

@@ -22,7 +22,20 @@ __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b
         const int l = L - i;
         if (r == 0ull) break;                             // step 1 + 5: the rest of the pulses sit on the last component
         const unsigned long long n0 = pvq_N(t, l - 1, k);
-        if (r < n0) { x[i] = 0.0; continue; }
+        if (r < n0) {
+            // a run of zeros: x_i' = 0 while r < N(l'-1, k).  N(m, k) grows with m, so the end of the run
+            // is the smallest m with N(m, k) > r, found by bisection (wide bands with a handful of
+            // pulses are the critical path of the leaf phase otherwise)
+            int lo = 1, hi = l - 1;                       // N(0, k) = 0 <= r, N(l-1, k) > r
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (pvq_N(t, mid, k) > r) hi = mid; else lo = mid + 1;
+            }
+            const int stop = L - lo;                      // first position whose remaining length is lo
+            for (; i < stop; ++i) x[i] = 0.0;
+            --i;
+            continue;
+        }
         const unsigned long long nlk = pvq_N(t, l, k);
         long long lo = 1, hi = k;
         while (lo < hi) {
@@ -149,11 +162,8 @@ __device__ __forceinline__ void warp_dequantize_gain_shape(const PvqTab& t, BitR
 //            normalise leaves, recombine mid/side, then apply the gain
 // Offsets in DNode are absolute positions in the CTA's ping-pong workspaces wsA / wsB.
 struct DNode {
-    unsigned long long u;      // leaf: Fischer index; internal: theta, then cos(theta) after phase B (double bits)
-    union {
-        int K;                 // leaf: pulses
-        double sn;             // internal: sin(theta), written by phase B
-    };
+    unsigned long long u;      // leaf: Fischer index; internal: theta (double bits)
+    int K;                     // leaf: pulses; internal: thetaTab entry (-1: evaluate cos / sin)
     short off, n, prev;        // workspace offset, length, previous node of the same band (-1: none)
     unsigned char capLog2, flags;
 };
@@ -229,15 +239,17 @@ __device__ __forceinline__ void grp_parse_gain_shape(const PvqTab& t, BitR& br, 
             if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
             const unsigned long long ti = br_get(br, aT);
             used += aT;
-            const double theta = dequantize_uniform(ti, aT) * 1.5707963267948966;
-            ms_alloc(aMs, theta, half, &aMid, &aSide);
+            double theta, l2t;
+            int entry;
+            theta_terms(t, ti, aT, &theta, &l2t, &entry);
+            ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
             double* oth = (nd.buf ? wsA : wsB) + nd.off;
             for (int i = lane; i < half; i += G) {       // children that get no bits stay zero
                 if (aMid <= 0) oth[i] = 0.0;
                 if (aSide <= 0) oth[hc + i] = 0.0;
             }
             dn.u = (unsigned long long)__double_as_longlong(theta);
-            dn.K = 0;
+            dn.K = entry;                                   // >= 0: cos / sin come from the table in phase C
             tail = dn_append<G>(nodes, nNodes, maxNodes, dn, err);
             if (tail < 0) break;
             if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
@@ -264,13 +276,7 @@ __device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, DNode* nodes,
     const int nWarps = nThreads >> 5;                      // node j -> warp j % nWarps, lane j / nWarps
     for (int i = (tid & 31) * nWarps + (tid >> 5); i < nNodes; i += nThreads) {
         const DNode nd = nodes[i];
-        if (!(nd.flags & DN_LEAF)) {                       // rotation of the recombine step, once per node
-            double sn, ct;
-            pm_sincos(__longlong_as_double((long long)nd.u), &sn, &ct);
-            nodes[i].u = (unsigned long long)__double_as_longlong(ct);
-            nodes[i].sn = sn;
-            continue;
-        }
+        if (!(nd.flags & DN_LEAF)) continue;
         int werr = 0;
         pvq_vector(t, nd.u, nd.n, nd.K, ((nd.flags & DN_BUF) ? wsB : wsA) + nd.off, &werr);
         if (werr) atomicOr(err, werr);
@@ -279,8 +285,8 @@ __device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, DNode* nodes,
 
 // Phase C for one band on one group of G lanes: out[0..L) <- gain * shape.  base as in phase A.
 template <int G>
-__device__ __forceinline__ void grp_finish_gain_shape(const DNode* nodes, const BandDec& bd, double* wsA, double* wsB,
-                                                       int base, double* out) {
+__device__ __forceinline__ void grp_finish_gain_shape(const double* thetaTab, const DNode* nodes, const BandDec& bd,
+                                                      double* wsA, double* wsB, int base, double* out) {
     const int lane = threadIdx.x & (G - 1);
     const unsigned gmask = grp_mask<G>();
     const int L = bd.L;
@@ -308,7 +314,14 @@ __device__ __forceinline__ void grp_finish_gain_shape(const DNode* nodes, const 
         }
         // recombine (coder/gain_shape_quantize.py:449-463)
         const int mid = n / 2, half = (n + 1) / 2, hc = (1 << nd.capLog2) / 2;
-        const double ct = __longlong_as_double((long long)nd.u), sn = nd.sn, r2 = sqrt(2.0);
+        double ct, sn;
+        if (nd.K >= 0 && thetaTab) {
+            ct = thetaTab[4 * nd.K + 2];
+            sn = thetaTab[4 * nd.K + 3];
+        } else {
+            pm_sincos(__longlong_as_double((long long)nd.u), &sn, &ct);
+        }
+        const double r2 = sqrt(2.0);
         double ss = 0.0;
         for (int i = lane; i < half; i += G) {
             const double m = oth[i], s = oth[hc + i];

@@ -21,3 +21,16 @@ v = np.array(buf[:], dtype=np.float64)
 for base, tag in ((0, "long"), (16, "short")):
     tot = v[base:base + 16].sum()
     print(tag, "total Mcycles %.1f" % (tot / 1e6), {nm: round(v[base + i] / tot, 3) for i, nm in enumerate(names)})
+
+# decoder
+d_out, off, _ = engine.encode_device(ctx, d.reshape(-1), [nb] * S, [n] * S)
+dnames = ["header(t0)", "A parse", "B leaves", "C recombine", "sbr"]
+for it in range(2):
+    _lib.lib.pac_debug_phases_dec(buf)
+    engine.decode_device(ctx, d_out, off)
+    torch.cuda.synchronize()
+_lib.lib.pac_debug_phases_dec(buf)
+v = np.array(buf[:], dtype=np.float64)
+for base, tag in ((0, "dec long"), (16, "dec short")):
+    tot = v[base:base + 16].sum()
+    print(tag, "total Mcycles %.1f (front only; the IMDCT tail is not counted)" % (tot / 1e6), {nm: round(v[base + i] / tot, 3) for i, nm in enumerate(dnames)})
