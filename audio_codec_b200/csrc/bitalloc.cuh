@@ -38,38 +38,50 @@ __device__ __forceinline__ void warp_bit_alloc(double budget, int maxMant, int n
     int bits = 0;
     bool flagged = false;
     int nflip = 0, count = 0;
+    // Everything up to the needle level depends only on WHICH bands are still valid, and most passes
+    // (the nflip search) leave that set unchanged: keep the pass state keyed on the valid mask.
+    unsigned vmCached = 0u, pm = 0u;
+    bool haveCache = false, posf = false;
+    double ropt = 0.0, fr = 0.0;
+    int nD = 0, rank = 0;
     while (true) {
         const bool valid = act && !flagged;
         const unsigned vm = __ballot_sync(FULL, valid);
-        int Ni = valid ? nl : 0;
+        if (!haveCache || vm != vmCached) {
+            haveCache = true;
+            vmCached = vm;
+            int Ni = valid ? nl : 0;
 #pragma unroll
-        for (int o = 16; o; o >>= 1) Ni += __shfl_xor_sync(FULL, Ni, o);
-        double N = Ni == 0 ? 1e-12 : (double)Ni;
-        // compacted products in band order -> NumPy-ordered sum on lane 0
-        int pos = __popc(vm & ((1u << lane) - 1));
-        if (valid) tmp[pos] = (double)nl * s;
-        __syncwarp();
-        double S = 0.0;
-        if (lane == 0) S = np_sum_small(tmp, __popc(vm));
-        S = __shfl_sync(FULL, S, 0);
-        __syncwarp();
-        double ropt = budget / N + (1.0 / 6.2) * (s - S / N);
-        double fr = ropt - floor(ropt) - 0.5;
-        const bool posf = valid && fr > 0.0;
-        const unsigned pm = __ballot_sync(FULL, posf);
-        const int nD = __popc(pm);
+            for (int o = 16; o; o >>= 1) Ni += __shfl_xor_sync(FULL, Ni, o);
+            double N = Ni == 0 ? 1e-12 : (double)Ni;
+            // compacted products in band order -> NumPy-ordered sum on lane 0
+            int pos = __popc(vm & ((1u << lane) - 1));
+            if (valid) tmp[pos] = (double)nl * s;
+            __syncwarp();
+            double S = 0.0;
+            if (lane == 0) S = np_sum_small(tmp, __popc(vm));
+            S = __shfl_sync(FULL, S, 0);
+            __syncwarp();
+            ropt = budget / N + (1.0 / 6.2) * (s - S / N);
+            fr = ropt - floor(ropt) - 0.5;
+            posf = valid && fr > 0.0;
+            pm = __ballot_sync(FULL, posf);
+            nD = __popc(pm);
+            // rank of this lane's fraction among the positive fractions (ascending, ties by band)
+            rank = 0;
+            for (unsigned m = pm; m;) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                const double fj = __shfl_sync(FULL, fr, j);
+                if (fj < fr || (fj == fr && j < lane)) ++rank;
+            }
+        }
         if (nflip > nD) {
             nflip -= 1;                                   // bits unchanged this pass
         } else {
             double level = 0.0;
             if (nflip > 0) {
-                // value of rank nflip-1 among the positive fractions (ascending)
-                int rank = 0;
-                for (int j = 0; j < 32; ++j) {
-                    double fj = __shfl_sync(FULL, fr, j);
-                    bool pj = (pm >> j) & 1u;
-                    if (pj && (fj < fr || (fj == fr && j < lane))) ++rank;
-                }
+                // value of rank nflip-1 among the positive fractions
                 unsigned hit = __ballot_sync(FULL, posf && rank == nflip - 1);
                 level = __shfl_sync(FULL, fr, __ffs(hit) - 1);
             }
