@@ -161,21 +161,22 @@ def mdct_leg(ctx, peak):
         y = mdct.imdct_ola(X, 2048, _lib.W_SINE, ctx)
         torch.cuda.synchronize()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-        tf = ti = 0.0
-        it = 5
-        for _ in range(it):
+        tfs, tis = [], []
+        for _ in range(7):
             ev[0].record()
             X = mdct.mdct_frames(x, 2048, _lib.W_SINE, ctx)
             ev[1].record()
             y = mdct.imdct_ola(X, 2048, _lib.W_SINE, ctx)
             ev[2].record()
             torch.cuda.synchronize()
-            tf += ev[0].elapsed_time(ev[1]) / it
-            ti += ev[1].elapsed_time(ev[2]) / it
+            tfs.append(ev[0].elapsed_time(ev[1]))
+            tis.append(ev[1].elapsed_time(ev[2]))
+        tf, ti = float(np.median(tfs)), float(np.median(tis))      # median of 7: allocator hiccups out
         algo = 2 * f * 1024 * x.element_size() * 2
         err = float((y[:, 1024:-1024] - x[:, 1024:-1024]).abs().max())
         out[name] = {"fwd_ms": tf, "inv_ms": ti, "fwd_gbs": algo / tf / 1e6, "inv_gbs": algo / ti / 1e6,
-                     "fwd_frac": algo / tf / 1e6 / peak, "inv_frac": algo / ti / 1e6 / peak, "tdac_max_err": err}
+                     "fwd_frac": algo / tf / 1e6 / peak, "inv_frac": algo / ti / 1e6 / peak, "tdac_max_err": err,
+                     "fwd_ms_all": [round(v, 3) for v in tfs], "inv_ms_all": [round(v, 3) for v in tis]}
         del x, X, y
     return out
 
