@@ -155,7 +155,7 @@ template <typename T>
 static int launch_inv_stream(pac_ctx* ctx, const void* X, int nRows, int nFrames, int window, void* y,
                              long long rowStride, cudaStream_t st) {
     const PacTables<T>& t = tabs<T>(ctx);
-    constexpr int W = MsCfg<T>::WARPS;
+    constexpr int W = MsCfg<T>::WARPS_INV;
     const T* win = window == PAC_WIN_NONE ? nullptr : t.win_long + (size_t)window * 2048;
     const int seg = stream_seg(nRows, nFrames + 1, W), segs = (nFrames + 1 + seg - 1) / seg;
     const long long units = (long long)nRows * segs;

@@ -23,8 +23,12 @@
 #define MS_TILE 544                              // values per half of the tile: 512 + skew (complex view: 544 entries)
 
 template <typename T> struct MsCfg;
-template <> struct MsCfg<float> { static constexpr int WARPS = 16; };
-template <> struct MsCfg<double> { static constexpr int WARPS = 7; };
+#ifndef MS_INV_WARPS_F64
+#define MS_INV_WARPS_F64 8
+#endif
+// warps per CTA (one CTA per SM): bounded by shared memory (forward, fp64 inverse) and registers
+template <> struct MsCfg<float> { static constexpr int WARPS = 16, WARPS_INV = 16; };
+template <> struct MsCfg<double> { static constexpr int WARPS = 7, WARPS_INV = MS_INV_WARPS_F64; };
 
 // 16-point DFT in registers, natural order in and out (4 x 4 Cooley-Tukey).
 template <typename T> __device__ __forceinline__ void bfly16(cplx<T>* u) {
@@ -232,14 +236,14 @@ k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int
                     const T a2 = E1[a] * (SYM ? w1 : W1[a]), a3 = E1[512 + b] * (SYM ? w0 : W1[512 + b]);
                     t.x = a0 - a1; t.y = -a2 - a3;
                 }
-                u[it] = cmul(t, tb.tw[n]);
+                u[it] = cmul(t, MsRun<T>::ldc(tb.tw + n));
             }
             warp_fft512<T>(u, tileRe, tb, lane);
             // post-twiddle into the staging arrays (even / odd output indices)
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
                 const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
-                const cplx<T> y = cmul(u[r], tb.tw[k]);
+                const cplx<T> y = cmul(u[r], MsRun<T>::ldc(tb.tw + k));
                 tileRe[MS_OSK(k)] = scale * y.x;               // out[2k]
                 tileIm[MS_OSK(Q - 1 - k)] = -scale * y.y;      // out[M - 1 - 2k]
             }
@@ -268,15 +272,15 @@ k_mdct_fwd_stream(const T* __restrict__ x, long long rowStride, int nFrames, int
 // The windowed second half of the previous frame stays in registers (each lane re-reads exactly
 // the positions it wrote).
 template <typename T> __host__ __device__ constexpr size_t ms_inv_smem_bytes() {
-    return sizeof(T) * ((size_t)2048 + 2 * 1024 + (size_t)MsCfg<T>::WARPS * (1024 + 2 * MS_TILE));
+    return sizeof(T) * ((size_t)2048 + 2 * 1024 + (size_t)MsCfg<T>::WARPS_INV * (1024 + 2 * MS_TILE));
 }
 
 template <typename T>
-__global__ void __launch_bounds__(MsCfg<T>::WARPS * 32, 1)
+__global__ void __launch_bounds__(MsCfg<T>::WARPS_INV * 32, 1)
 k_imdct_ola_stream(const T* __restrict__ X, int nFrames, int seg, int segsPerRow, long long nUnits,
                    const T* __restrict__ winG, const cplx<T>* __restrict__ twG, const cplx<T>* __restrict__ rootsG,
                    T* __restrict__ y, long long rowStride, int vec) {
-    constexpr int M = 1024, Q = 512, W = MsCfg<T>::WARPS;
+    constexpr int M = 1024, Q = 512, W = MsCfg<T>::WARPS_INV;
     constexpr int NV = MsBlock<T>::NV, PER = MsBlock<T>::PER, L = MsRun<T>::L;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     MsTables<T> tb;
@@ -309,13 +313,13 @@ k_imdct_ola_stream(const T* __restrict__ X, int nFrames, int seg, int segsPerRow
                 for (int it = 0; it < 16; ++it) {
                     const int n = lane + 32 * it;
                     const cplx<T> t = {Ei[n], Ei[512 + Q - 1 - n]};      // {X[2n], X[M-1-2n]}
-                    u[it] = cmul(t, tb.tw[n]);
+                    u[it] = cmul(t, MsRun<T>::ldc(tb.tw + n));
                 }
                 warp_fft512<T>(u, Ev, tb, lane);
 #pragma unroll
                 for (int r = 0; r < 16; ++r) {
                     const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
-                    const cplx<T> v = cmul(u[r], tb.tw[k]);
+                    const cplx<T> v = cmul(u[r], MsRun<T>::ldc(tb.tw + k));
                     Ev[MS_OSK(k)] = v.x;                   // xv[2k]
                     Ov[MS_OSK(Q - 1 - k)] = -v.y;          // xv[M - 1 - 2k]
                 }
