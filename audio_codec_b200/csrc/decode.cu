@@ -32,6 +32,7 @@ k_walk(const unsigned char* __restrict__ buf, const long long* __restrict__ stre
     if (s >= nStreams) return;
     const long long end = streamOff[s + 1], bufEnd = streamOff[nStreams];
     const long long base = cbOff ? cbOff[s] : 0;
+    const int limit = cbOff ? (int)(cbOff[s + 1] - cbOff[s]) : 0;
     const unsigned long long addr0 = (unsigned long long)buf;
     long long pos = streamOff[s] + headerBytes;
     int n = 0;
@@ -53,8 +54,8 @@ k_walk(const unsigned char* __restrict__ buf, const long long* __restrict__ stre
                 const unsigned char* q = &win[warp][pos - w0];
                 const unsigned nb = (unsigned)q[0] | ((unsigned)q[1] << 8) | ((unsigned)q[2] << 16) | ((unsigned)q[3] << 24);
                 if (pos + 4 + (long long)nb > end) { done = true; break; }      // truncated block
-                if (payOff) {
-                    payOff[base + n] = pos + 4;
+                if (payOff && n < limit) {                 // a damaged stream may end on a partial block: its
+                    payOff[base + n] = pos + 4;             // extra record must not land in the next stream's slot
                     payBytes[base + n] = (int)nb;
                 }
                 ++n;
