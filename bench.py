@@ -181,12 +181,57 @@ def mdct_leg(ctx, peak):
     return out
 
 
-def fp32_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out64, off64, audio_s, steps):
+def smr_leg(ctx, peak):
+    """The metric's "SMR HBM GB/s": psychoac.CalcSMRs batched over synthetic frames (N = 2048; one CTA
+    per frame: Hann FFT, tonal maskers, masked threshold, per-band SMR).  Buffers are fp64 as the
+    reference's arrays are (16 384 B samples + 8 192 B lines + 4 B scale in, 8 B x bands out per
+    frame); the arithmetic is fp64 or fp32.  Compute bound (>= 250 flop/B): the fraction of HBM peak
+    is reported for the record next to frames/s."""
+    import ctypes as C
+    import torch
+    from audio_codec_b200 import _lib, mdct
+    F = int(os.environ.get("PAC_SMR_FRAMES", 1 << 17))
+    g = torch.Generator(device="cuda").manual_seed(422)
+    t = torch.arange(2048, device="cuda", dtype=torch.float64) / FS
+    f0 = 55.0 * 2 ** (5 * torch.rand((F, 1), generator=g, device="cuda", dtype=torch.float64))
+    x = 0.25 * torch.sin(2 * np.pi * f0 * t) + 0.1 * torch.sin(2 * np.pi * 3.1 * f0 * t + 1.0)
+    x += 0.01 * torch.randn((F, 2048), generator=g, device="cuda", dtype=torch.float64)
+    X = mdct.mdct_frames(x.reshape(1, -1)[:, :(F + 1) * 1024].contiguous(), 2048, _lib.W_SINE, ctx)
+    lines = (X.reshape(-1, 1024)[:F] * 4.0).contiguous()      # hop-1024 frames of the same signal, scaled by 2^2
+    assert lines.shape[0] == F
+    scale = torch.full((F,), 2, dtype=torch.int32, device="cuda")
+    nl, lo = ctx.bands()
+    nB = len(nl)
+    smr = torch.empty((F, nB), dtype=torch.float64, device="cuda")
+    lo_p, nl_p = (C.c_int * nB)(*[int(v) for v in lo]), (C.c_int * nB)(*[int(v) for v in nl])
+    out = {"workload": f"{F} frames, N=2048, {nB} bands, fp64 buffers ({F * (16384 + 8192) / 1e9:.1f} GB in, larger than L2)"}
+    algo = F * (2048 * 8 + 1024 * 8 + 4 + 8 * nB)
+    for name, dt in (("f32", 0), ("f64", 1)):
+        def run():
+            _lib.check(_lib.lib.pac_calc_smr(ctx.h, dt, C.c_void_p(x.data_ptr()), C.c_void_p(lines.data_ptr()),
+                                             C.c_void_p(scale.data_ptr()), F, 2048, nB, lo_p, nl_p,
+                                             C.c_void_p(smr.data_ptr()), None, _lib.stream_ptr()))
+        run()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            run()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ms = float(np.median(ts))
+        out[name] = {"ms": ms, "frames_per_s": F / (ms * 1e-3), "gbs": algo / ms / 1e6, "frac": algo / ms / 1e6 / peak}
+    return out
+
+
+def variant_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out64, off64, audio_s, steps, rate=None, precision="f64"):
     """The fp32 fast path (precision="f32": transforms + psychoacoustic model in fp32) on the same
     workload, device resident, plus its code-mismatch rate against the fp64 encoding just made
     (fraction of (block, channel) records whose bytes differ, first 8 streams)."""
     import torch
-    ctx = _lib.Context(sample_rate=FS, n_channels=2, rate_kbps=RATE, device=local, precision="f32")
+    ctx = _lib.Context(sample_rate=FS, n_channels=2, rate_kbps=rate or RATE, device=local, precision=precision)
     d_out = torch.empty_like(d_out64)
     d_dec = None
     for _ in range(2):
@@ -206,6 +251,11 @@ def fp32_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out64, off64, audio_s, step
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
+    res = {"value": audio_s * steps / (ms * 1e-3), "unit": "audio-s/s (this rank)", "k_encode_ms": float(np.mean(enc_ms)),
+           "k_decode_ms": float(np.mean(dec_ms))}
+    if precision == "f64":                      # another bit rate: no comparison with the 128 kb/s encoding
+        res["config"] = f"{rate or RATE} kb/s/ch, SBR {'on' if (rate or RATE) < 128 else 'off'}, fp64, same streams"
+        return res
     k = min(8, len(nbs))
     a = d_out[:int(off[k])].cpu().numpy().tobytes()
     b = d_out64[:int(off64[k])].cpu().numpy().tobytes()
@@ -215,10 +265,10 @@ def fp32_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out64, off64, audio_s, step
         rb = engine.block_records(b[int(off64[s]):int(off64[s + 1])])
         tot += max(len(ra), len(rb))
         diff += max(len(ra), len(rb)) - sum(1 for x, y in zip(ra, rb) if x == y)
-    return {"value": audio_s * steps / (ms * 1e-3), "unit": "audio-s/s (this rank)", "k_encode_ms": float(np.mean(enc_ms)),
-            "k_decode_ms": float(np.mean(dec_ms)), "record_mismatch_rate": diff / max(tot, 1),
-            "mismatch_sample": f"{tot} (block, channel) records of the first {k} streams vs the fp64 encoding",
-            "tolerance": "MDCT/SMR 1e-5 rel, PCM <= 1 LSB (tests/test_fp32_gpu.py)"}
+    res.update({"record_mismatch_rate": diff / max(tot, 1),
+                "mismatch_sample": f"{tot} (block, channel) records of the first {k} streams vs the fp64 encoding",
+                "tolerance": "MDCT/SMR 1e-5 rel, PCM <= 1 LSB (tests/test_fp32_gpu.py)"})
+    return res
 
 
 def main():
@@ -228,8 +278,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
-    ap.add_argument("--no-mdct", action="store_true", help="skip the MDCT/IMDCT bandwidth leg (BASELINE config 2)")
-    ap.add_argument("--no-fp32", action="store_true", help="skip the fp32 fast-path leg")
+    ap.add_argument("--no-mdct", action="store_true", help="skip the MDCT/IMDCT and SMR bandwidth legs (BASELINE config 2)")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the fp32 fast-path and 96 kb/s legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -352,8 +402,10 @@ def main():
             pass
         if not args.no_mdct:
             line["mdct"] = mdct_leg(ctx, peak)
+            line["smr"] = smr_leg(ctx, peak)
         if not args.no_fp32:
-            line["fp32"] = fp32_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out, off, audio_s, args.steps)
+            line["fp32"] = variant_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out, off, audio_s, args.steps, precision="f32")
+            line["rate96"] = variant_leg(engine, _lib, local, d_pcm, nbs, hdr, d_out, off, audio_s, args.steps, rate=96)
         if not args.no_cpu:
             cs = float(os.environ.get("PAC_CPU_SECONDS", 12.0))
             sample = pcm[0, :, :int(cs * FS)].cpu().numpy()
