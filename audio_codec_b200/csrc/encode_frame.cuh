@@ -276,27 +276,43 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
     __syncthreads();
 
     PHASE(6);
-    // (6) frame header + band payload positions (coder/pacfile.py:363-447), thread 0
-    if (tid == 0) {
-        BitW bw = {S.blockbuf, *bpos};
-        bw_put(bw, (unsigned long long)scale, dev->nScaleBits);
-        int declared = dev->nScaleBits;
-        if (dev->useVQ)
-            for (int b = 0; b < nB; ++b) bw_put(bw, S.ba[b] ? S.ba[b] - 1 : 0, dev->nMantSizeBits);
-        for (int b = 0; b < nB; ++b) {
-            if (!dev->useVQ) {
-                bw_put(bw, S.ba[b] ? S.ba[b] - 1 : 0, dev->nMantSizeBits);
-                bw_put(bw, (unsigned long long)S.sfb[b], dev->nScaleBits);
-            }
-            int u = S.ba[b] ? S.used[b] : 0;
-            S.capOff[b] = bw.pos;                         // reuse: destination bit position of band b
-            bw.pos += u;
-            declared += dev->nMantSizeBits + dev->nScaleBits;
-            if (S.ba[b]) declared += (sbr && bands.omitted[b]) ? S.ba[b] : S.ba[b] * bands.nLines[b];
+    // (6) frame header + band payload positions (coder/pacfile.py:363-447): every field has a fixed
+    //     width, so one warp places them with a scan over the bands (lane = band)
+    if (warp == 0) {
+        const int pos0 = *bpos, nS = dev->nScaleBits, nM = dev->nMantSizeBits;
+        const bool vq = dev->useVQ;
+        const bool act = lane < nB;
+        const int bab = act ? S.ba[lane] : 0;
+        const int u = bab ? S.used[lane] : 0;
+        const int hdrBits = vq ? 0 : nM + nS;              // block-FP interleaves [ba, sf] with the mantissas
+        int len = act ? hdrBits + u : 0, inc = len;
+        int decl = act ? nM + nS + (bab ? ((sbr && bands.omitted[lane]) ? bab : bab * bands.nLines[lane]) : 0) : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
         }
-        *bpos = bw.pos;
-        S.misc[2] = declared;
-        S.misc[5] = scale;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) decl += __shfl_xor_sync(0xffffffffu, decl, o);
+        const int base = pos0 + nS + (vq ? nB * nM : 0);
+        const int mine = base + inc - len;                 // start of this band's [header,] payload
+        if (lane == 0) bw_put_at(S.blockbuf, pos0, (unsigned long long)scale, nS);
+        if (act) {
+            const unsigned long long code = bab ? bab - 1 : 0;
+            if (vq) {
+                bw_put_at(S.blockbuf, pos0 + nS + lane * nM, code, nM);
+            } else {
+                bw_put_at(S.blockbuf, mine, code, nM);
+                bw_put_at(S.blockbuf, mine + nM, (unsigned long long)S.sfb[lane], nS);
+            }
+            S.capOff[lane] = mine + hdrBits;              // reuse: destination bit position of band b
+        }
+        const int total = __shfl_sync(0xffffffffu, inc, 31);
+        if (lane == 0) {
+            *bpos = base + total;
+            S.misc[2] = nS + decl;
+            S.misc[5] = scale;
+        }
     }
     __syncthreads();
     PHASE(7);
