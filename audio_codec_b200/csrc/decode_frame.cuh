@@ -77,7 +77,48 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     const PacBands& bands = isLong ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
     DPHASE_T0(isLong);
-    // (1) frame header: overall scale, bit allocations (+ BFP scale factors): thread 0
+    // (1) frame header: overall scale, bit allocations (+ BFP scale factors).  VQ streams carry the
+    //     allocations as fixed-width fields up front: one warp reads them in parallel (lane = band) and
+    //     places the band payloads with a scan.  Block-FP interleaves them with the mantissas: thread 0.
+    if (dev->useVQ) {
+        if (warp == 0) {
+            const int pos0 = S.misc[3], nS = dev->nScaleBits, nM = dev->nMantSizeBits;
+            const bool act = lane < nB;
+            BitR br = {S.rec, (long long)pos0 + nS + (long long)lane * nM, recBits, DEC_REC_MAX};
+            int bab = 0;
+            if (act) {
+                const int v = (int)br_get(br, nM);
+                bab = v ? v + 1 : 0;
+                S.ba[lane] = bab;
+            }
+            const bool om = act && isLong && bands.omitted[lane];
+            const bool sbr = isLong && dev->useSBR && __any_sync(0xffffffffu, om && bab != 0);    // coder/pacfile.py:660-664
+            const int len = bab ? bab * ((sbr && om) ? 1 : bands.nLines[lane]) : 0;
+            int cap = 0;
+            if (act) { cap = 1; while (cap < bands.nLines[lane]) cap <<= 1; }
+            int inc = len, cinc = cap;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o), tc = __shfl_up_sync(0xffffffffu, cinc, o);
+                if (lane >= o) { inc += t; cinc += tc; }
+            }
+            const int base = pos0 + nS + nB * nM;
+            if (act) {
+                S.bandPos[lane] = base + inc - len;
+                S.capOff[lane] = cinc - cap;
+            }
+            const int total = __shfl_sync(0xffffffffu, inc, 31), ctot = __shfl_sync(0xffffffffu, cinc, 31);
+            if (lane == 0) {
+                BitR b0 = {S.rec, pos0, recBits, DEC_REC_MAX};
+                S.misc[5] = (int)br_get(b0, nS);
+                S.misc[6] = sbr;
+                S.misc[7] = 0;
+                S.misc[3] = base + total;
+                S.capOff[nB] = ctot;
+                if ((long long)base + total > recBits) atomicOr(err, PVQ_ERR_STACK);
+            }
+        }
+    } else
     if (tid == 0) {
         BitR br = {S.rec, S.misc[3], recBits, DEC_REC_MAX};
         S.misc[7] = 0;
