@@ -132,8 +132,42 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
 #undef PH_IS_LONG
     // (4) bit budget + allocation (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145)
     if (tid < nB) S.nlEff[tid] = (sbr && bands.omitted[tid]) ? 1 : bands.nLines[tid];
+    if (warp == 1) {                                       // pow2 workspace offsets of the bands (static layout)
+        int c = 0;
+        if (lane < nB) { c = 1; while (c < bands.nLines[lane]) c <<= 1; }
+        int ci = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int tc = __shfl_up_sync(0xffffffffu, ci, o);
+            if (lane >= o) ci += tc;
+        }
+        if (lane < nB) S.capOff[lane] = ci - c;
+        if (lane == nB - 1) S.capOff[nB] = ci;
+    }
+    // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
+    // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
+    double* wsA = isLong ? S.xs : S.lines + 256;
+    double* wsB = isLong ? S.fb : S.lines + 512;
     __syncthreads();
-    if (warp == 0) {
+    if (warp != 0) {
+        // while warp 0 runs the (serial) allocation: gain and normalised copy of every band - they do
+        // not depend on the allocation.  SBR-omitted bands carry one value: mean |fftLines| (codec.py:508-510)
+        if (dev->useVQ && S.capOff[nB] <= (isLong ? 2048 : 256)) {
+            for (int b = warp - 1; b < nB; b += ENC_NT / 32 - 1) {
+                const bool env = sbr && bands.omitted[b];
+                const int L = env ? 1 : bands.nLines[b];
+                const double* x = S.lines + bands.lower[b];
+                const double envVal = env ? (S.env[b] * up) / (double)bands.nLines[b] : 0.0;
+                double ss = 0.0;
+                if (env) ss = lane == 0 ? envVal * envVal : 0.0;
+                else for (int i = lane; i < L; i += 32) ss += x[i] * x[i];
+                const double gain = sqrt(warp_sum(ss));
+                if (gain != 0.0)
+                    for (int i = lane; i < L; i += 32) wsA[S.capOff[b] + i] = (env ? envVal : x[i]) / gain;
+                if (lane == 0) S.bandEnc[b].gain = gain;
+            }
+        }
+    } else {
         int nfb = H;
         if (!sbr) {
             if (cur) nfb = (int)(1.45 * H);
@@ -145,26 +179,21 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
         budget -= (double)(dev->nMantSizeBits * nB);
         warp_bit_alloc(budget, dev->maxMantBits, nB, S.nlEff, S.smr, S.tmp, S.ba);
         __syncwarp();
-        // per-band private bit buffer (words) and pow2 workspace offsets: exclusive scans over the bands
-        int w = 0, c = 0;
-        if (lane < nB) {
-            const int bits = S.ba[lane] * S.nlEff[lane];
-            w = (bits + 31) / 32 + 3;                     // slack: a 64-bit put may straddle
-            c = 1;
-            while (c < bands.nLines[lane]) c <<= 1;
-        }
-        int wi = w, ci = c;
+        // per-band private bit buffers (words): exclusive scan over the bands
+        int w = 0;
+        if (lane < nB) w = (S.ba[lane] * S.nlEff[lane] + 31) / 32 + 3;      // slack: a 64-bit put may straddle
+        int wi = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int tw = __shfl_up_sync(0xffffffffu, wi, o), tc = __shfl_up_sync(0xffffffffu, ci, o);
-            if (lane >= o) { wi += tw; ci += tc; }
+            const int tw = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += tw;
         }
-        if (lane < nB) { S.wordOff[lane] = wi - w; S.capOff[lane] = ci - c; }
+        if (lane < nB) S.wordOff[lane] = wi - w;
         if (lane == nB - 1) {
             S.wordOff[nB] = wi;
-            S.capOff[nB] = ci;
-            if (wi > BAND_WORDS || ci > (isLong ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
+            if (wi > BAND_WORDS || S.capOff[nB] > (isLong ? 2048 : 256)) atomicOr(err, PVQ_ERR_STACK);
         }
+        if (lane == 0) S.misc[6] = 0;                      // node pool fill
     }
 
     PHASE(3);
@@ -174,49 +203,33 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
     if (S.wordOff[nB] > BAND_WORDS || S.capOff[nB] > (isLong ? 2048 : 256)) return 0;
     PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
     int* yws = reinterpret_cast<int*>(S.mk);              // masked threshold is dead from here on
-    // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
-    // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
-    double* wsA = isLong ? S.xs : S.lines + 256;
-    double* wsB = isLong ? S.fb : S.lines + 512;
     if (dev->useVQ) {
-        // roots: one warp per band: gain, normalised copy of the band, root node of its split tree
-        if (tid == 0) S.misc[6] = 0;
-        __syncthreads();
-        for (int b = warp; b < nB; b += ENC_NT / 32) {
-            if (!S.ba[b]) continue;
-            const bool env = sbr && bands.omitted[b];       // one value: mean |fftLines| (coder/codec.py:508-510)
+        // roots: one thread per band (gain and normalised copy are in place): bit split, root node
+        if (tid < nB && S.ba[tid]) {
+            const int b = tid;
+            const bool env = sbr && bands.omitted[b];
             const int L = env ? 1 : bands.nLines[b], R = env ? S.ba[b] : S.ba[b] * bands.nLines[b];
-            const double* x = S.lines + bands.lower[b];
-            const double envVal = env ? (S.env[b] * up) / (double)bands.nLines[b] : 0.0;
             int bg, bs;
             gs_alloc(pt, R, L, &bg, &bs);
-            double ss = 0.0;
-            if (env) ss = lane == 0 ? envVal * envVal : 0.0;
-            else for (int i = lane; i < L; i += 32) ss += x[i] * x[i];
-            const double gain = sqrt(warp_sum(ss));
+            const double gain = S.bandEnc[b].gain;
             int root = -1;
             if (gain != 0.0 && bs != 0) {
-                for (int i = lane; i < L; i += 32) wsA[S.capOff[b] + i] = (env ? envVal : x[i]) / gain;
-                if (lane == 0) {
-                    root = atomicAdd(&S.misc[6], 1);
-                    if (root < ENC_MAX_NODES) {
-                        TNode r;
-                        r.val = 0ull; r.bits = bs; r.K = -2; r.off = (short)S.capOff[b]; r.n = (short)L;
-                        r.kid[0] = r.kid[1] = -1;
-                        r.capLog2 = (unsigned char)(31 - __clz(S.capOff[b + 1] - S.capOff[b]));
-                        r.buf = 0; r.band = (unsigned char)b; r.w = 0; r.logSlot = -1; r.pad = 0;
-                        S.nodes[root] = r;
-                    } else {
-                        atomicOr(err, PVQ_ERR_STACK);
-                        root = -1;
-                    }
+                root = atomicAdd(&S.misc[6], 1);
+                if (root < ENC_MAX_NODES) {
+                    TNode r;
+                    r.val = 0ull; r.bits = bs; r.K = -2; r.off = (short)S.capOff[b]; r.n = (short)L;
+                    r.kid[0] = r.kid[1] = -1;
+                    r.capLog2 = (unsigned char)(31 - __clz(S.capOff[b + 1] - S.capOff[b]));
+                    r.buf = 0; r.band = (unsigned char)b; r.w = 0; r.logSlot = -1; r.pad = 0;
+                    S.nodes[root] = r;
+                } else {
+                    atomicOr(err, PVQ_ERR_STACK);
+                    root = -1;
                 }
             }
-            if (lane == 0) {
-                BandEnc be;
-                be.gain = gain; be.bg = bg; be.bs = bs; be.root = root; be.L = L;
-                S.bandEnc[b] = be;
-            }
+            BandEnc be;
+            be.gain = gain; be.bg = bg; be.bs = bs; be.root = root; be.L = L;
+            S.bandEnc[b] = be;
         }
         PHASE(4);
         // levels: the nodes of one tree depth of all bands - vector work on one warp per node,
