@@ -16,7 +16,7 @@
 #define PAC_HALF_SHORT 128
 #define PAC_SUBFRAMES 8
 #define PAC_PVQ_LMAX 1024
-#define PAC_THETA_BITS 12
+#define PAC_THETA_BITS 16
 #define PAC_EPS 2.220446049250313e-16   // np.finfo(float).eps
 
 // window shapes (coder/window.py:14-92, selected by coder/codec.py:30-44)
