@@ -79,6 +79,7 @@ struct DecArgs {
     const long long* payOff;   // [nCb]
     const int* payBytes;       // [nCb]
     double* frames;            // [nCb][2048] windowed block output before block overlap-add
+    long long cb0;             // first channel-block of this launch
     int* err;
 };
 
@@ -89,7 +90,7 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a) {
     DecSmem S;
     dec_smem_carve(smem_raw, S);
     const int tid = threadIdx.x;
-    const int cb = blockIdx.x;
+    const long long cb = (long long)blockIdx.x + a.cb0;
     int nBytes = a.payBytes[cb];
     if (nBytes > DEC_REC_MAX) {
         if (tid == 0) atomicOr(a.err, PVQ_ERR_STACK);
@@ -112,7 +113,7 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a) {
                 decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err);
         }
     }
-    double* dst = a.frames + (long long)cb * 2048;
+    double* dst = a.frames + cb * 2048;
     for (int i = tid; i < 2048; i += DEC_NT) dst[i] = S.y[i];
 }
 
@@ -126,9 +127,9 @@ __device__ __forceinline__ short double_to_pcm(double x) {
 // Output block b of (stream, channel) = tail of written block b-1 + head of written block b;
 // the final block is the overlap flush (coder/pacfile.py:247-251, :289-295).
 __global__ void k_ola(const double* __restrict__ frames, const long long* __restrict__ cbOff,
-                      const long long* __restrict__ pcmOff, int nStreams, int C, short* __restrict__ pcm) {
+                      const long long* __restrict__ pcmOff, int nStreams, int C, short* __restrict__ pcm, long long g0) {
     // grid: one CTA per (output block, channel) over all streams; find the stream by binary search
-    const long long g = blockIdx.x;        // index over sum_s (nBlk_s + 1) * C
+    const long long g = blockIdx.x + g0;   // index over sum_s (nBlk_s + 1) * C
     int lo = 0, hi = nStreams;
     // output blocks of stream s start at pcmOff[s]/1024 (pcmOff counts samples over all channels)
     while (hi - lo > 1) {
@@ -190,9 +191,14 @@ extern "C" int pac_decode_plan(pac_ctx* ctx, const unsigned char* d_pac, const l
     return 0;
 }
 
-extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off,
-                                  int n_streams, short* d_pcm, long long pcm_capacity, long long* h_pcm_off,
-                                  int* h_err, void* stream) {
+// The decoder proper.  chunks: stream boundaries [c0 = 0, c1, ..., n_streams] (nullptr: one chunk); the
+// kernels are launched per chunk and chunkEv[c] is recorded after chunk c, so a caller can move
+// finished chunks off the device while the rest decodes; with h_copy_dst the chunk's PCM is sent to
+// that host buffer on copyStream as soon as its event fires (the host-buffer entry point).
+int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off,
+                               int n_streams, short* d_pcm, long long pcm_capacity, long long* h_pcm_off,
+                               int* h_err, void* stream, const int* chunks, int n_chunks, cudaEvent_t* chunkEv,
+                               cudaStream_t copyStream, short* h_copy_dst) {
     if (!ctx || !h_stream_off || !h_pcm_off) return PAC_ERR_ARG;
     if (n_streams <= 0) return 0;
     if (!d_pac || !d_pcm) return PAC_ERR_ARG;
@@ -229,29 +235,51 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
     // a trailing partial block (fewer than C channel-blocks) lands in the C spare slots and is ignored
     k_walk<<<(S + WALK_WARPS - 1) / WALK_WARPS, WALK_WARPS * 32, 0, st>>>(d_pac, (long long*)(sb + oSOff), S, pac_header_bytes(ctx), nullptr,
                                             (long long*)(sb + oCbOff), (long long*)(sb + oPay), (int*)(sb + oPayB));
-    if (nCb > 0) {
+    const int oneChunk[2] = {0, S};
+    if (!chunks) { chunks = oneChunk; n_chunks = 1; }
+    for (int c = 0; c < n_chunks; ++c) {
+    const int s0 = chunks[c], s1 = chunks[c + 1];
+    const long long cb0 = cbOff[s0], nCbC = cbOff[s1] - cb0;
+    if (nCbC > 0) {
         DecArgs a;
         a.buf = d_pac; a.payOff = (long long*)(sb + oPay); a.payBytes = (int*)(sb + oPayB);
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
+        a.cb0 = cb0;
         size_t smem = dec_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
         PAC_CHECK(cudaFuncSetAttribute(k_decode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PAC_CHECK(cudaFuncSetAttribute(k_decode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        cudaEventRecord(ctx->ev[2], st);
-        if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);
-        else k_decode<double><<<(unsigned)nCb, DEC_NT, smem, st>>>(ctx->dev, a);
-        cudaEventRecord(ctx->ev[3], st);
-        ctx->evValid[1] = 1;
+        if (c == 0) cudaEventRecord(ctx->ev[2], st);      // pac_last_kernel_ms: the first chunk (the only one unless chunked)
+        if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nCbC, DEC_NT, smem, st>>>(ctx->dev, a);
+        else k_decode<double><<<(unsigned)nCbC, DEC_NT, smem, st>>>(ctx->dev, a);
+        if (c == 0) { cudaEventRecord(ctx->ev[3], st); ctx->evValid[1] = 1; }
         PAC_CHECK(cudaGetLastError());
     }
-    const long long nOut = pcmOff[S] / 1024;
-    k_ola<<<(unsigned)nOut, 256, 0, st>>>((const double*)(sb + oFrames), (long long*)(sb + oCbOff),
-                                          (long long*)(sb + oPcmOff), S, C, d_pcm);
+    const long long g0 = pcmOff[s0] / 1024, nOut = pcmOff[s1] / 1024 - g0;
+    if (nOut > 0)
+        k_ola<<<(unsigned)nOut, 256, 0, st>>>((const double*)(sb + oFrames), (long long*)(sb + oCbOff),
+                                              (long long*)(sb + oPcmOff), S, C, d_pcm, g0);
     PAC_CHECK(cudaGetLastError());
+    if (chunkEv) {
+        PAC_CHECK(cudaEventRecord(chunkEv[c], st));
+        if (h_copy_dst && pcmOff[s1] > pcmOff[s0]) {
+            PAC_CHECK(cudaStreamWaitEvent(copyStream, chunkEv[c], 0));
+            PAC_CHECK(cudaMemcpyAsync(h_copy_dst + pcmOff[s0], d_pcm + pcmOff[s0], (size_t)(pcmOff[s1] - pcmOff[s0]) * sizeof(short),
+                                      cudaMemcpyDeviceToHost, copyStream));
+        }
+    }
+    }
     int err = 0;
     PAC_CHECK(cudaMemcpyAsync(&err, sb + oErr, sizeof(int), cudaMemcpyDeviceToHost, st));
     PAC_CHECK(cudaStreamSynchronize(st));
     if (h_err) *h_err = err;
     return err ? PAC_ERR_SOFT : 0;
+}
+
+extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off,
+                                  int n_streams, short* d_pcm, long long pcm_capacity, long long* h_pcm_off,
+                                  int* h_err, void* stream) {
+    return pac_decode_streams_chunked(ctx, d_pac, h_stream_off, n_streams, d_pcm, pcm_capacity, h_pcm_off, h_err, stream,
+                                      nullptr, 0, nullptr, nullptr, nullptr);
 }
 
 #ifdef PAC_PHASE_TIMING

@@ -17,6 +17,7 @@ static int copy_streams(pac_ctx* ctx) {
         PAC_CHECK(cudaStreamCreateWithFlags(&ctx->cp[i], cudaStreamNonBlocking));
         PAC_CHECK(cudaEventCreateWithFlags(&ctx->cpEv[i], cudaEventDisableTiming));
     }
+    for (int i = 0; i < 8; ++i) PAC_CHECK(cudaEventCreateWithFlags(&ctx->chunkEv[i], cudaEventDisableTiming));
     ctx->cpReady = 1;
     return 0;
 }
@@ -25,23 +26,31 @@ static int copy_streams(pac_ctx* ctx) {
 // compression); PAC_HOST_CHUNK_MB overrides it (tests use tiny chunks).
 static long long chunk_mb() {
     const char* e = getenv("PAC_HOST_CHUNK_MB");
-    const double v = e ? atof(e) : 32.0;
-    return (long long)((v > 0.0 ? v : 32.0) * 1048576.0);
+    const double v = e ? atof(e) : 24.0;
+    return (long long)((v > 0.0 ? v : 24.0) * 1048576.0);
 }
 
-// Chunk boundaries (in streams): up to 4 chunks of roughly equal size by `weight`, one chunk for
+// Chunk boundaries (in streams): up to 6 chunks whose sizes ramp up and down (1 2 3 3 2 1), so the
+// first upload and the last download - the two copies nothing can hide - are short; one chunk for
 // small batches (the per-call latency of the stream walk and the scans would dominate).
 static std::vector<int> chunk_bounds(const std::vector<long long>& weight, long long minChunk) {
     const int n = (int)weight.size();
     long long tot = 0;
     for (long long w : weight) tot += w;
-    int k = (int)std::min<long long>(4, std::max<long long>(1, tot / std::max<long long>(1, minChunk)));
+    int k = (int)std::min<long long>(6, std::max<long long>(1, tot / std::max<long long>(1, minChunk)));
     k = std::min(k, n);
+    static const int ramp[7][6] = {{0}, {1}, {1, 1}, {1, 2, 1}, {1, 2, 2, 1}, {1, 2, 3, 2, 1}, {1, 2, 3, 3, 2, 1}};
+    int rsum = 0;
+    for (int c = 0; c < k; ++c) rsum += ramp[k][c];
     std::vector<int> b{0};
     long long acc = 0;
+    int racc = ramp[k][0];
     for (int s = 0; s < n; ++s) {
         acc += weight[s];
-        if ((int)b.size() < k && acc * k >= tot * (long long)b.size() && s + 1 < n) b.push_back(s + 1);
+        if ((int)b.size() < k && acc * rsum >= tot * racc && s + 1 < n) {
+            b.push_back(s + 1);
+            racc += ramp[k][b.size() - 1];
+        }
     }
     b.push_back(n);
     return b;
@@ -140,24 +149,14 @@ extern "C" int pac_decode_host(pac_ctx* ctx, const unsigned char* h_pac, const l
     for (int s = 0; s < n_streams; ++s) weight[s] = off[s + 1] - off[s];
     const std::vector<int> cb = chunk_bounds(weight, std::max<long long>(1, chunk_mb() / 6));
     const int nChunks = (int)cb.size() - 1;
-    int soft = 0, errAll = 0;
-    std::vector<long long> coff, poff;
-    for (int c = 0; c < nChunks; ++c) {
-        const int s0 = cb[c], ns = cb[c + 1] - s0;
-        coff.assign(off.begin() + s0, off.begin() + s0 + ns + 1);
-        poff.assign(ns + 1, 0);
-        const long long p0 = h_pcm_off[s0], total = h_pcm_off[s0 + ns] - p0;
-        int e = 0;
-        rc = pac_decode_streams(ctx, (const unsigned char*)dIn, coff.data(), ns, (short*)dOut + p0, total, poff.data(), &e,
-                                stream);
-        if (rc != 0 && rc != PAC_ERR_SOFT) return rc;
-        if (poff[ns] != total) return PAC_ERR_ARG;
-        soft |= rc == PAC_ERR_SOFT;
-        errAll |= e;
-        // pac_decode_streams has synchronised st: the chunk is complete, send it down behind the next one
-        PAC_CHECK(cudaMemcpyAsync(h_pcm + p0, (short*)dOut + p0, (size_t)total * sizeof(short), cudaMemcpyDeviceToHost,
-                                  ctx->cp[1]));
-    }
+    // one walk, the kernels launched per chunk with an event after each: the copy stream takes every
+    // finished chunk down while the next ones decode
+    PAC_CHECK(cudaStreamSynchronize(ctx->cp[1]));         // the staging buffer may still be draining from the last call
+    int errAll = 0;
+    rc = pac_decode_streams_chunked(ctx, (const unsigned char*)dIn, off.data(), n_streams, (short*)dOut, totalAll, h_pcm_off,
+                                    &errAll, stream, cb.data(), nChunks, ctx->chunkEv, ctx->cp[1], h_pcm);
+    if (rc != 0 && rc != PAC_ERR_SOFT) return rc;
+    const int soft = rc == PAC_ERR_SOFT;
     PAC_CHECK(cudaStreamSynchronize(ctx->cp[1]));
     if (h_err) *h_err = errAll;
     return soft ? PAC_ERR_SOFT : 0;

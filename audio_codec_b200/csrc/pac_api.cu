@@ -422,7 +422,10 @@ extern "C" void pac_destroy(pac_ctx* c) {
     for (int i = 0; i < 2; ++i) if (c->io[i]) cudaFree(c->io[i]);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(c->ev[i]);
     if (c->cpReady)
+    {
         for (int i = 0; i < 2; ++i) { cudaStreamDestroy(c->cp[i]); cudaEventDestroy(c->cpEv[i]); }
+        for (int i = 0; i < 8; ++i) cudaEventDestroy(c->chunkEv[i]);
+    }
     delete c;
 }
 

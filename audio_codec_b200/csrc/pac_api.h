@@ -19,6 +19,7 @@ struct pac_ctx {
     size_t ioBytes[2];
     cudaStream_t cp[2];  // copy streams of the host-buffer entry points (created on first use)
     cudaEvent_t cpEv[2];
+    cudaEvent_t chunkEv[8];
     int cpReady;
     cudaEvent_t ev[4];   // around k_encode and k_decode, for pac_last_kernel_ms
     int evValid[2];
@@ -32,3 +33,9 @@ int pac_pinned(pac_ctx* ctx, size_t bytes, void** out);
 int pac_io(pac_ctx* ctx, int which, size_t bytes, void** out);
 // window table of length N (kind: PAC_W_*, Ns = short length for the Edler shapes)
 int pac_window_table(pac_ctx* ctx, int kind, int N, int Ns, double alpha, const double** d, const float** f);
+
+// decode.cu: pac_decode_streams launched per chunk of streams, chunkEv[c] recorded after chunk c
+int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off, int n_streams,
+                               short* d_pcm, long long pcm_capacity, long long* h_pcm_off, int* h_err, void* stream,
+                               const int* chunks, int n_chunks, cudaEvent_t* chunkEv, cudaStream_t copyStream,
+                               short* h_copy_dst);
