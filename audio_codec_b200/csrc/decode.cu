@@ -8,11 +8,13 @@
 //   k_ola       overlap-add consecutive blocks and quantise to 16-bit PCM
 //               (coder/pacfile.py:289-295, coder/pcmfile.py:118-147)
 #include <string.h>
+#include <algorithm>
 #include <vector>
 #include "decode_frame.cuh"
 #include "pac_api.h"
 
 extern "C" int pac_header_bytes(const pac_ctx* ctx);
+#define DEC_BATCH_CB 65536       // channel-blocks per k_parse / k_decode pair (bounds the parse scratch: 18 KB each)
 
 // pass 0: count channel-blocks; pass 1: record payload offsets (absolute, past the prefix).
 // The prefix chain is serial, but its cost is the memory latency per hop: one WARP per stream
@@ -79,13 +81,128 @@ struct DecArgs {
     const long long* payOff;   // [nCb]
     const int* payBytes;       // [nCb]
     double* frames;            // [nCb][2048] windowed block output before block overlap-add
+    long long bufBytes;        // size of buf
     long long cb0;             // first channel-block of this launch
     int* err;
 };
 
+// Header + split-tree parse of VQ streams, ahead of k_decode.  A CTA takes PARSE_CBS channel-blocks;
+// lane = channel-block, so a warp parses the SAME band of 32 blocks at a time (similar trees, little
+// divergence) and the serial, latency-bound chains (field widths depend on the angles just read)
+// run thousands at a time per SM instead of 17 per CTA.  Writes CbPre + the node lists.
+#define PARSE_CBS 32
+#define PARSE_NT 256
+__global__ void __launch_bounds__(PARSE_NT)
+k_parse(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbPre* __restrict__ pre,
+        DNode* __restrict__ nodesG) {
+    __shared__ unsigned short s_pos[PRE_SLOTS][PARSE_CBS];
+    __shared__ unsigned char s_ba[PRE_SLOTS][PARSE_CBS];
+    __shared__ int s_cnt[PAC_SUBFRAMES][PARSE_CBS];
+    __shared__ unsigned char s_flags[PARSE_CBS], s_sbr[PARSE_CBS], s_scale[PAC_SUBFRAMES][PARSE_CBS];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int local = blockIdx.x * PARSE_CBS + lane;          // index into this launch's CbPre / node regions
+    const bool have = local < nCb;
+    const long long cb = cbBase + local;
+    // bit reader over global memory: 8-byte words at absolute alignment (the record may start at any byte)
+    BitR br = {nullptr, 0, 0, 0};
+    long long bit0 = 0;
+    int nBytes = 0;
+    if (have) {
+        nBytes = min(a.payBytes[cb], DEC_REC_MAX);
+        const unsigned char* rec = a.buf + a.payOff[cb];
+        const unsigned long long ad = (unsigned long long)rec;
+        const unsigned char* al = rec - (ad & 7ull);
+        bit0 = 8LL * (long long)(ad & 7ull);
+        br.p = al; br.end = bit0 + 8LL * nBytes;
+        const long long room = (a.buf + a.bufBytes) - al;     // readable bytes from the aligned base
+        br.cap = (int)min((long long)(DEC_REC_MAX + 16), room & ~7LL);
+        if (br.cap < (int)(ad & 7ull) + nBytes) {             // the record ends inside the buffer's last partial word
+            br.p = rec; br.end = 8LL * nBytes; br.cap = 0; bit0 = 0;
+        }
+    }
+    const int nS = dev->nScaleBits, nM = dev->nMantSizeBits;
+    if (warp == 0) {
+        unsigned char fl = 0, sbrF = 0;
+        for (int f = 0; f < PAC_SUBFRAMES; ++f) s_cnt[f][lane] = 0;
+        if (have && nBytes > 0) {
+            br.pos = bit0;
+            fl = (unsigned char)(br_get(br, 3) | 0x80u);      // last, cur, next (coder/pacfile.py:196-198)
+            const bool cur = (fl >> 1) & 1;
+            const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+            const int nB = bands.nBands, nF = cur ? PAC_SUBFRAMES : 1;
+            for (int f = 0; f < nF; ++f) {
+                s_scale[f][lane] = (unsigned char)br_get(br, nS);
+                bool anyOm = false;
+                for (int b = 0; b < nB; ++b) {
+                    const int v = (int)br_get(br, nM);
+                    const int bab = v ? v + 1 : 0;
+                    s_ba[f * nB + b][lane] = (unsigned char)bab;
+                    anyOm |= !cur && bands.omitted[b] && bab != 0;
+                }
+                const bool sbr = !cur && dev->useSBR && anyOm;            // coder/pacfile.py:660-664
+                if (sbr) sbrF = 1;
+                long long p = br.pos;
+                for (int b = 0; b < nB; ++b) {
+                    s_pos[f * nB + b][lane] = (unsigned short)min(p - bit0, 65535LL);   // past the end: reads zeros
+                    const int bab = s_ba[f * nB + b][lane];
+                    if (bab) p += (long long)bab * ((sbr && bands.omitted[b]) ? 1 : bands.nLines[b]);
+                }
+                if (p > br.end) atomicOr(a.err, PVQ_ERR_STACK);
+                br.pos = p;
+            }
+        }
+        s_flags[lane] = fl;
+        s_sbr[lane] = sbrF;
+    }
+    __syncthreads();
+    const unsigned char fl = s_flags[lane];
+    if (fl & 0x80u) {
+        const bool cur = (fl >> 1) & 1, sbr = s_sbr[lane] != 0;
+        const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+        const int nB = bands.nBands, nSlots = cur ? PAC_SUBFRAMES * nB : nB;
+        PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
+        CbPre* pc = pre + local;
+        DNode* region = nodesG + (size_t)local * PRE_NODES_PER_CB;
+        // widest bands first (they are the long chains)
+        for (int q = warp; q < PRE_SLOTS; q += PARSE_NT / 32) {
+            if (q >= nSlots) break;
+            const int f = q / nB, b = nB - 1 - (q - f * nB), slot = f * nB + b;
+            const int bb = s_ba[slot][lane];
+            if (!bb) continue;
+            int cap = 1, base = 0;
+            while (cap < bands.nLines[b]) cap <<= 1;
+            for (int j = 0; j < b; ++j) { int c = 1; while (c < bands.nLines[j]) c <<= 1; base += c; }
+            const bool env = sbr && bands.omitted[b];          // one envelope value (coder/codec.py:111-132)
+            br.pos = bit0 + s_pos[slot][lane];
+            int werr = 0;
+            double gain;
+            short tail;
+            thread_parse_band(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], base, cap,
+                              region + (cur ? f * PRE_SHORT_NODES : 0), &s_cnt[f][lane],
+                              cur ? PRE_SHORT_NODES : DEC_MAX_NODES, &gain, &tail, &werr);
+            if (werr) atomicOr(a.err, werr);
+            pc->gain[slot] = gain;
+            pc->tail[slot] = tail;
+        }
+    }
+    __syncthreads();
+    if (warp == 0 && have) {
+        CbPre* pc = pre + local;
+        const bool cur = (fl >> 1) & 1;
+        const int nB = cur ? dev->shortBands.nBands : dev->longBands.nBands, nSlots = (fl & 0x80u) ? (cur ? PAC_SUBFRAMES * nB : nB) : 0;
+        for (int q = 0; q < nSlots; ++q) pc->ba[q] = s_ba[q][lane];
+        for (int f = 0; f < PAC_SUBFRAMES; ++f) {
+            pc->nNodes[f] = (unsigned short)min(s_cnt[f][lane], 65535);
+            pc->scale[f] = s_scale[f][lane];
+        }
+        pc->sbr = s_sbr[lane];
+        pc->flags = fl;
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(DEC_NT, 3)
-k_decode(const PacDev* __restrict__ dev, DecArgs a) {
+k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbPre* __restrict__ preAll, const DNode* __restrict__ nodesG) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DecSmem S;
     dec_smem_carve(smem_raw, S);
@@ -96,21 +213,25 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a) {
         if (tid == 0) atomicOr(a.err, PVQ_ERR_STACK);
         nBytes = DEC_REC_MAX;
     }
+    const CbPre* pre = preAll ? preAll + blockIdx.x : nullptr;
+    const DNode* region = preAll ? nodesG + (size_t)blockIdx.x * PRE_NODES_PER_CB : nullptr;
     const unsigned char* src = a.buf + a.payOff[cb];
-    for (int i = tid; i < nBytes; i += DEC_NT) S.rec[i] = src[i];
+    if (!pre) for (int i = tid; i < nBytes; i += DEC_NT) S.rec[i] = src[i];
     for (int i = tid; i < 2048; i += DEC_NT) S.y[i] = 0.0;
     __syncthreads();
     const long long recBits = 8LL * nBytes;
-    const bool last = (S.rec[0] >> 7) & 1, cur = (S.rec[0] >> 6) & 1, nxt = (S.rec[0] >> 5) & 1;
+    const unsigned char b0 = pre ? (unsigned char)(pre->flags << 5) : S.rec[0];
+    const bool last = (b0 >> 7) & 1, cur = (b0 >> 6) & 1, nxt = (b0 >> 5) & 1;
     if (tid == 0) S.misc[3] = 3;
     __syncthreads();
     if (nBytes > 0) {
         if (!cur) {
             int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err);
+            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err, pre, region, 0);
         } else {
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err);
+                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err, pre,
+                                            region ? region + sf * PRE_SHORT_NODES : nullptr, sf);
         }
     }
     double* dst = a.frames + cb * 2048;
@@ -224,6 +345,11 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     size_t oPayB = carve((size_t)(nCb + C) * sizeof(int));
     size_t oErr = carve(sizeof(int));
     size_t oFrames = carve((size_t)nCb * 2048 * sizeof(double));
+    // VQ streams: k_parse output for one batch of channel-blocks at a time (reused batch after batch)
+    const bool vq = ctx->cfg.use_vq != 0;
+    const long long batchCb = vq ? std::min<long long>(nCb, DEC_BATCH_CB) : 0;
+    size_t oPre = carve((size_t)batchCb * sizeof(CbPre));
+    size_t oNodes = carve((size_t)batchCb * PRE_NODES_PER_CB * sizeof(DNode));
     void* scr = nullptr;
     if ((rc = pac_scratch(ctx, o, &scr))) return rc;
     unsigned char* sb = (unsigned char*)scr;
@@ -244,13 +370,20 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
         DecArgs a;
         a.buf = d_pac; a.payOff = (long long*)(sb + oPay); a.payBytes = (int*)(sb + oPayB);
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
-        a.cb0 = cb0;
+        a.bufBytes = h_stream_off[S];
         size_t smem = dec_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
         PAC_CHECK(cudaFuncSetAttribute(k_decode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PAC_CHECK(cudaFuncSetAttribute(k_decode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (c == 0) cudaEventRecord(ctx->ev[2], st);      // pac_last_kernel_ms: the first chunk (the only one unless chunked)
-        if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nCbC, DEC_NT, smem, st>>>(ctx->dev, a);
-        else k_decode<double><<<(unsigned)nCbC, DEC_NT, smem, st>>>(ctx->dev, a);
+        for (long long q0 = 0; q0 < nCbC; q0 += vq ? batchCb : nCbC) {
+            const long long nq = vq ? std::min(batchCb, nCbC - q0) : nCbC;
+            a.cb0 = cb0 + q0;
+            CbPre* dPre = vq ? (CbPre*)(sb + oPre) : nullptr;
+            DNode* dNodes = vq ? (DNode*)(sb + oNodes) : nullptr;
+            if (vq) k_parse<<<(unsigned)((nq + PARSE_CBS - 1) / PARSE_CBS), PARSE_NT, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre, dNodes);
+            if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dNodes);
+            else k_decode<double><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dNodes);
+        }
         if (c == 0) { cudaEventRecord(ctx->ev[3], st); ctx->evValid[1] = 1; }
         PAC_CHECK(cudaGetLastError());
     }

@@ -21,6 +21,22 @@ static __device__ unsigned long long g_pac_dphase[32];
 #define DEC_GROUP 32              // lanes per band in the per-band phases (8 / 16 measured slower: divergent groups of a warp serialise)
 #define DEC_MAX_NODES 512         // split-tree nodes per frame (a 128 kb/s long frame has ~150); sized for 3 CTAs per SM
 
+// What k_parse (decode.cu) leaves per channel-block for k_decode: slot = sub-frame * nBands + band.
+#define PRE_SLOTS 48              // 17 long bands, or 8 sub-frames x 6 short bands
+#define PRE_SHORT_NODES 96        // node capacity of one short sub-frame (a long frame has DEC_MAX_NODES)
+#define PRE_NODES_PER_CB (PAC_SUBFRAMES * PRE_SHORT_NODES)
+struct CbPre {
+    double gain[PRE_SLOTS];           // inv-mu-law gain * L of the band
+    short tail[PRE_SLOTS];            // last node of the band in the frame's list (-1: shape = ones)
+    unsigned char ba[PRE_SLOTS];      // bit allocation
+    unsigned short nNodes[PAC_SUBFRAMES];
+    unsigned char scale[PAC_SUBFRAMES];
+    unsigned char sbr;                // long frame of an SBR stream with coded envelope bands
+    unsigned char flags;              // bit 2 last, 1 cur, 0 next transient; bit 7: record present
+    unsigned char pad[6];
+};
+static_assert(PRE_NODES_PER_CB >= DEC_MAX_NODES, "node region per channel-block");
+
 struct DecSmem {
     unsigned char* rec;   // [DEC_REC_MAX] payload bytes
     double* lines;        // [1024] dequantised MDCT lines of the current frame
@@ -69,7 +85,8 @@ __device__ __forceinline__
 static __device__ __noinline__
 #endif
 int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long recBits,
-                                                bool isLong, int* err) {
+                                                bool isLong, int* err, const CbPre* __restrict__ pre,
+                                                const DNode* __restrict__ preNodes, int sf) {
     DecSmem S;
     dec_smem_carve(raw, S);
     const int H = isLong ? PAC_HALF_LONG : PAC_HALF_SHORT;
@@ -80,6 +97,40 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     // (1) frame header: overall scale, bit allocations (+ BFP scale factors).  VQ streams carry the
     //     allocations as fixed-width fields up front: one warp reads them in parallel (lane = band) and
     //     places the band payloads with a scan.  Block-FP interleaves them with the mantissas: thread 0.
+    if (pre) {
+        // header and split trees were parsed by k_parse: bring this frame's part into shared memory
+        const int n = min((int)pre->nNodes[sf], isLong ? DEC_MAX_NODES : PRE_SHORT_NODES);
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(preNodes);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(S.nodes);
+        for (int i = tid; i < n * (int)(sizeof(DNode) / 8); i += DEC_NT) dst[i] = src[i];
+        if (warp == 0) {
+            const bool act = lane < nB;
+            const bool sbr = isLong && pre->sbr;
+            const int slot = sf * nB + lane;
+            int cap = 0;
+            if (act) { cap = 1; while (cap < bands.nLines[lane]) cap <<= 1; }
+            int cinc = cap;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int tc = __shfl_up_sync(0xffffffffu, cinc, o);
+                if (lane >= o) cinc += tc;
+            }
+            if (act) {
+                S.ba[lane] = pre->ba[slot];
+                S.capOff[lane] = cinc - cap;
+                BandDec bd;
+                bd.gain = pre->gain[slot]; bd.tail = pre->tail[slot];
+                bd.L = (sbr && bands.omitted[lane]) ? 1 : bands.nLines[lane];
+                S.bd[lane] = bd;
+            }
+            if (lane == nB - 1) S.capOff[nB] = cinc;
+            if (lane == 0) {
+                S.misc[5] = pre->scale[sf];
+                S.misc[6] = sbr;
+                S.misc[7] = n;
+            }
+        }
+    } else
     if (dev->useVQ) {
         if (warp == 0) {
             const int pos0 = S.misc[3], nS = dev->nScaleBits, nM = dev->nMantSizeBits;
@@ -172,7 +223,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
         constexpr int G = DEC_GROUP;
         const int grp = tid / G;
         // phase A is scalar: one THREAD per band, bands dealt round-robin to the warps (<= 4 per warp)
-        {
+        if (!pre) {
             const int b = lane * (DEC_NT / 32) + warp;
             const int bb = b < nB ? S.ba[b] : 0;
             if (bb) {
@@ -262,11 +313,12 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
 // adds its windowed IMDCT into y[yOff .. yOff+N).
 template <int N, typename T>
 __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, long long recBits, int shape, int yOff,
-                             int* err) {
+                             int* err, const CbPre* __restrict__ pre = nullptr, const DNode* __restrict__ preNodes = nullptr,
+                             int sf = 0) {
     constexpr int Q = N / 4;
     const int tid = threadIdx.x;
     const bool isLong = N == PAC_NLONG;
-    const int scale = decode_front(dev, S.raw, recBits, isLong, err);
+    const int scale = decode_front(dev, S.raw, recBits, isLong, err, pre, preNodes, sf);
     // (4) undo the overall scale, IMDCT, synthesis window (coder/codec.py:85-89)
     // T = float: the transform runs in fp32 (fast path; PCM within 1 LSB of the fp64 result).
     const PacTables<T>& t = psy_tabs<T>(dev);

@@ -167,7 +167,7 @@ struct DNode {
     short off, n, prev;        // workspace offset, length, previous node of the same band (-1: none)
     unsigned char capLog2, flags;
 };
-enum { DN_LEAF = 1, DN_ROOT = 2, DN_BUF = 4 };
+enum { DN_LEAF = 1, DN_ROOT = 2, DN_BUF = 4, DN_ZMID = 8, DN_ZSIDE = 16 };   // Z*: that child got no bits (reads as zeros)
 
 struct BandDec {               // per band, written by phase A (lane 0), read by phase C
     double gain;
@@ -270,6 +270,72 @@ __device__ __forceinline__ void grp_parse_gain_shape(const PvqTab& t, BitR& br, 
     }
 }
 
+// Phase A as its own kernel (k_parse, decode.cu): ONE THREAD per band, the 32 lanes of a warp hold
+// the same band of 32 different channel-blocks, so the lanes run the same loop with similar trip
+// counts and thousands of these serial chains are in flight per SM.  Nodes go to the frame's list in
+// global memory (slots from a shared-memory counter); children without bits are flagged on the
+// parent (DN_ZMID / DN_ZSIDE) instead of zeroed, because the workspaces do not exist yet.
+__device__ __forceinline__ void thread_parse_band(const PvqTab& t, BitR& br, int R, int L, int base, int cap,
+                                                  DNode* __restrict__ nodes, int* nNodes, int maxNodes, double* gainOut,
+                                                  short* tailOut, int* err) {
+    int bg, bs, tail = -1;
+    gs_alloc(t, R, L, &bg, &bs);
+    if (bs != 0) {
+        ParseNode st[24];
+        int sp = 0, used = 0;
+        st[sp++] = {(short)base, (short)cap, (short)L, 0, bs, 1};
+        while (sp > 0) {
+            const ParseNode nd = st[--sp];
+            DNode dn;
+            dn.off = nd.off; dn.n = nd.n; dn.prev = (short)tail;
+            dn.capLog2 = (unsigned char)(31 - __clz((int)nd.cap));
+            dn.flags = (unsigned char)((nd.buf ? DN_BUF : 0) | (nd.root ? DN_ROOT : 0));
+            int aMid = 0, aSide = 0;
+            const bool leaf = nd.bits <= PVQ_SPLIT_BITS;
+            if (leaf) {
+                long long K;
+                int w;
+                pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+                dn.u = br_get(br, w);
+                dn.K = (int)K;
+                dn.flags |= DN_LEAF;
+                used += w;
+            } else {
+                const int half = (nd.n + 1) / 2;
+                int aT, aMs;
+                gs_alloc(t, nd.bits, half, &aT, &aMs);
+                if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+                const unsigned long long ti = br_get(br, aT);
+                used += aT;
+                double theta, l2t;
+                int entry;
+                theta_terms(t, ti, aT, &theta, &l2t, &entry);
+                ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
+                dn.u = (unsigned long long)__double_as_longlong(theta);
+                dn.K = entry;
+                dn.flags |= (unsigned char)((aMid <= 0 ? DN_ZMID : 0) | (aSide <= 0 ? DN_ZSIDE : 0));
+            }
+            const int slot = atomicAdd(nNodes, 1);
+            if (slot >= maxNodes) { *err |= PVQ_ERR_STACK; tail = -1; break; }
+            nodes[slot] = dn;
+            tail = slot;
+            if (leaf) continue;
+            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
+            const int half = (nd.n + 1) / 2, hc = nd.cap / 2;
+            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, 0};
+            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid, 0};
+        }
+        bg += bs - used;
+    }
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    if (bg < 0) bg = 0;
+    const unsigned long long gi = br_get(br, bg);
+    const double gq = dequantize_uniform(gi, bg);
+    const double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
+    *gainOut = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
+    *tailOut = (short)tail;
+}
+
 // Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...
 __device__ __forceinline__ void cta_decode_leaves(const PvqTab& t, DNode* nodes, int nNodes, double* wsA,
                                                   double* wsB, int tid, int nThreads, int* err) {
@@ -324,7 +390,7 @@ __device__ __forceinline__ void grp_finish_gain_shape(const double* thetaTab, co
         const double r2 = sqrt(2.0);
         double ss = 0.0;
         for (int i = lane; i < half; i += G) {
-            const double m = oth[i], s = oth[hc + i];
+            const double m = (nd.flags & DN_ZMID) ? 0.0 : oth[i], s = (nd.flags & DN_ZSIDE) ? 0.0 : oth[hc + i];
             const double l = (m * ct + s * sn) / r2;
             const double r = (m * ct - s * sn) / r2;
             if (i < mid) { cur[i] = l; ss += l * l; }      // odd n: the padded last element of left is dropped
