@@ -14,7 +14,7 @@
 #include "pac_api.h"
 
 extern "C" int pac_header_bytes(const pac_ctx* ctx);
-#define DEC_BATCH_CB 65536       // channel-blocks per k_parse / k_decode pair (bounds the parse scratch: 18 KB each)
+#define DEC_BATCH_CB 65536       // channel-blocks per k_hdr / k_dequant / k_decode round (bounds the scratch: 32 KB each)
 
 // pass 0: count channel-blocks; pass 1: record payload offsets (absolute, past the prefix).
 // The prefix chain is serial, but its cost is the memory latency per hop: one WARP per stream
@@ -86,123 +86,130 @@ struct DecArgs {
     int* err;
 };
 
-// Header + split-tree parse of VQ streams, ahead of k_decode.  A CTA takes PARSE_CBS channel-blocks;
-// lane = channel-block, so a warp parses the SAME band of 32 blocks at a time (similar trees, little
-// divergence) and the serial, latency-bound chains (field widths depend on the angles just read)
-// run thousands at a time per SM instead of 17 per CTA.  Writes CbPre + the node lists.
-#define PARSE_CBS 32
-#define PARSE_NT 256
-__global__ void __launch_bounds__(PARSE_NT)
-k_parse(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbPre* __restrict__ pre,
-        DNode* __restrict__ nodesG) {
-    __shared__ unsigned short s_pos[PRE_SLOTS][PARSE_CBS];
-    __shared__ unsigned char s_ba[PRE_SLOTS][PARSE_CBS];
-    __shared__ int s_cnt[PAC_SUBFRAMES][PARSE_CBS];
-    __shared__ unsigned char s_flags[PARSE_CBS], s_sbr[PARSE_CBS], s_scale[PAC_SUBFRAMES][PARSE_CBS];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int local = blockIdx.x * PARSE_CBS + lane;          // index into this launch's CbPre / node regions
-    const bool have = local < nCb;
-    const long long cb = cbBase + local;
-    // bit reader over global memory: 8-byte words at absolute alignment (the record may start at any byte)
-    BitR br = {nullptr, 0, 0, 0};
-    long long bit0 = 0;
-    int nBytes = 0;
-    if (have) {
-        nBytes = min(a.payBytes[cb], DEC_REC_MAX);
-        const unsigned char* rec = a.buf + a.payOff[cb];
-        const unsigned long long ad = (unsigned long long)rec;
-        const unsigned char* al = rec - (ad & 7ull);
-        bit0 = 8LL * (long long)(ad & 7ull);
-        br.p = al; br.end = bit0 + 8LL * nBytes;
-        const long long room = (a.buf + a.bufBytes) - al;     // readable bytes from the aligned base
-        br.cap = (int)min((long long)(DEC_REC_MAX + 16), room & ~7LL);
-        if (br.cap < (int)(ad & 7ull) + nBytes) {             // the record ends inside the buffer's last partial word
-            br.p = rec; br.end = 8LL * nBytes; br.cap = 0; bit0 = 0;
-        }
+// ---- batched front end of VQ streams ------------------------------------------------------------
+// Bit reader over a record in global memory: 8-byte words at absolute alignment (a record may start
+// at any byte); bit0 = position of the record's first bit relative to the aligned base.
+__device__ __forceinline__ BitR rec_reader(const DecArgs& a, long long cb, int* nBytesOut, long long* bit0Out) {
+    const int nBytes = min(a.payBytes[cb], DEC_REC_MAX);
+    const unsigned char* rec = a.buf + a.payOff[cb];
+    const unsigned long long ad = (unsigned long long)rec;
+    const unsigned char* al = rec - (ad & 7ull);
+    long long bit0 = 8LL * (long long)(ad & 7ull);
+    BitR br = {al, bit0, bit0 + 8LL * nBytes, 0};
+    const long long room = (a.buf + a.bufBytes) - al;         // readable bytes from the aligned base
+    br.cap = (int)min((long long)(DEC_REC_MAX + 16), room & ~7LL);
+    if (br.cap < (int)(ad & 7ull) + nBytes) {                 // the record ends inside the buffer's last partial word
+        br.p = rec; br.end = 8LL * nBytes; br.cap = 0; bit0 = 0; br.pos = 0;
     }
-    const int nS = dev->nScaleBits, nM = dev->nMantSizeBits;
-    if (warp == 0) {
-        unsigned char fl = 0, sbrF = 0;
-        for (int f = 0; f < PAC_SUBFRAMES; ++f) s_cnt[f][lane] = 0;
-        if (have && nBytes > 0) {
-            br.pos = bit0;
-            fl = (unsigned char)(br_get(br, 3) | 0x80u);      // last, cur, next (coder/pacfile.py:196-198)
-            const bool cur = (fl >> 1) & 1;
-            const PacBands& bands = cur ? dev->shortBands : dev->longBands;
-            const int nB = bands.nBands, nF = cur ? PAC_SUBFRAMES : 1;
-            for (int f = 0; f < nF; ++f) {
-                s_scale[f][lane] = (unsigned char)br_get(br, nS);
-                bool anyOm = false;
-                for (int b = 0; b < nB; ++b) {
-                    const int v = (int)br_get(br, nM);
-                    const int bab = v ? v + 1 : 0;
-                    s_ba[f * nB + b][lane] = (unsigned char)bab;
-                    anyOm |= !cur && bands.omitted[b] && bab != 0;
-                }
-                const bool sbr = !cur && dev->useSBR && anyOm;            // coder/pacfile.py:660-664
-                if (sbr) sbrF = 1;
-                long long p = br.pos;
-                for (int b = 0; b < nB; ++b) {
-                    s_pos[f * nB + b][lane] = (unsigned short)min(p - bit0, 65535LL);   // past the end: reads zeros
-                    const int bab = s_ba[f * nB + b][lane];
-                    if (bab) p += (long long)bab * ((sbr && bands.omitted[b]) ? 1 : bands.nLines[b]);
-                }
-                if (p > br.end) atomicOr(a.err, PVQ_ERR_STACK);
-                br.pos = p;
-            }
-        }
-        s_flags[lane] = fl;
-        s_sbr[lane] = sbrF;
-    }
-    __syncthreads();
-    const unsigned char fl = s_flags[lane];
-    if (fl & 0x80u) {
-        const bool cur = (fl >> 1) & 1, sbr = s_sbr[lane] != 0;
-        const PacBands& bands = cur ? dev->shortBands : dev->longBands;
-        const int nB = bands.nBands, nSlots = cur ? PAC_SUBFRAMES * nB : nB;
-        PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
-        CbPre* pc = pre + local;
-        DNode* region = nodesG + (size_t)local * PRE_NODES_PER_CB;
-        // widest bands first (they are the long chains)
-        for (int q = warp; q < PRE_SLOTS; q += PARSE_NT / 32) {
-            if (q >= nSlots) break;
-            const int f = q / nB, b = nB - 1 - (q - f * nB), slot = f * nB + b;
-            const int bb = s_ba[slot][lane];
-            if (!bb) continue;
-            int cap = 1, base = 0;
-            while (cap < bands.nLines[b]) cap <<= 1;
-            for (int j = 0; j < b; ++j) { int c = 1; while (c < bands.nLines[j]) c <<= 1; base += c; }
-            const bool env = sbr && bands.omitted[b];          // one envelope value (coder/codec.py:111-132)
-            br.pos = bit0 + s_pos[slot][lane];
-            int werr = 0;
-            double gain;
-            short tail;
-            thread_parse_band(pt, br, env ? bb : bb * bands.nLines[b], env ? 1 : bands.nLines[b], base, cap,
-                              region + (cur ? f * PRE_SHORT_NODES : 0), &s_cnt[f][lane],
-                              cur ? PRE_SHORT_NODES : DEC_MAX_NODES, &gain, &tail, &werr);
-            if (werr) atomicOr(a.err, werr);
-            pc->gain[slot] = gain;
-            pc->tail[slot] = tail;
-        }
-    }
-    __syncthreads();
-    if (warp == 0 && have) {
-        CbPre* pc = pre + local;
+    *nBytesOut = nBytes;
+    *bit0Out = bit0;
+    return br;
+}
+
+// k_hdr: one thread per channel-block reads the block flags and every frame header (overall scale,
+// bit allocations) and places the band payloads (coder/pacfile.py:177-229).
+__global__ void __launch_bounds__(128)
+k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHdr* __restrict__ hdrs) {
+    const int local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (local >= nCb) return;
+    int nBytes;
+    long long bit0;
+    BitR br = rec_reader(a, cbBase + local, &nBytes, &bit0);
+    CbHdr* h = hdrs + local;
+    unsigned char fl = 0, sbrF = 0;
+    if (nBytes > 0) {
+        const int nS = dev->nScaleBits, nM = dev->nMantSizeBits;
+        fl = (unsigned char)(br_get(br, 3) | 0x80u);          // last, cur, next (coder/pacfile.py:196-198)
         const bool cur = (fl >> 1) & 1;
-        const int nB = cur ? dev->shortBands.nBands : dev->longBands.nBands, nSlots = (fl & 0x80u) ? (cur ? PAC_SUBFRAMES * nB : nB) : 0;
-        for (int q = 0; q < nSlots; ++q) pc->ba[q] = s_ba[q][lane];
-        for (int f = 0; f < PAC_SUBFRAMES; ++f) {
-            pc->nNodes[f] = (unsigned short)min(s_cnt[f][lane], 65535);
-            pc->scale[f] = s_scale[f][lane];
+        const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+        const int nB = bands.nBands, nF = cur ? PAC_SUBFRAMES : 1;
+        for (int f = 0; f < nF; ++f) {
+            h->scale[f] = (unsigned char)br_get(br, nS);
+            unsigned omMask = 0, baMask = 0;
+            for (int b = 0; b < nB; ++b) {
+                const int v = (int)br_get(br, nM);
+                const int bab = v ? v + 1 : 0;
+                h->ba[f * nB + b] = (unsigned char)bab;
+                if (bab) baMask |= 1u << b;
+                if (bands.omitted[b]) omMask |= 1u << b;
+            }
+            const bool sbr = !cur && dev->useSBR && (omMask & baMask);    // coder/pacfile.py:660-664
+            if (sbr) sbrF = 1;
+            long long p = br.pos;
+            for (int b = 0; b < nB; ++b) {
+                h->pos[f * nB + b] = (unsigned short)min(p - bit0, 65535LL);   // past the end: reads zeros
+                if ((baMask >> b) & 1) {
+                    const int bab = h->ba[f * nB + b];
+                    p += (long long)bab * ((sbr && bands.omitted[b]) ? 1 : bands.nLines[b]);
+                }
+            }
+            if (p > br.end) atomicOr(a.err, PVQ_ERR_STACK);
+            br.pos = p;
         }
-        pc->sbr = s_sbr[lane];
-        pc->flags = fl;
     }
+    h->sbr = sbrF;
+    h->flags = fl;
+}
+
+// k_dequant: one thread per (channel-block, band).  A CTA holds one band slot of DQ_NT consecutive
+// channel-blocks; CTAs are ordered widest band first so the long chains start first.  Slot q of a long
+// block is band nB-1-q; of a transient block, sub-frame q / 6, band 5 - q % 6.  Lines go to
+// lines[pre_line_index(cb, k)]; the workspaces are lane-interleaved the same way.
+#define DQ_NT 128
+__global__ void __launch_bounds__(DQ_NT)
+k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, int nChunks, CbHdr* __restrict__ hdrs,
+          double* __restrict__ lines, double* __restrict__ ws) {
+    const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
+    const int local = chunk * DQ_NT + threadIdx.x;
+    if (local >= nCb) return;
+    CbHdr* h = hdrs + local;
+    const unsigned char fl = h->flags;
+    if (!(fl & 0x80u)) return;
+    const bool cur = (fl >> 1) & 1;
+    const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+    const int nB = bands.nBands;
+    if (q >= (cur ? PAC_SUBFRAMES * nB : nB)) return;
+    const int f = q / nB, b = nB - 1 - (q - f * nB), slot = f * nB + b;
+    const bool sbr = h->sbr != 0, env = sbr && bands.omitted[b];
+    const int bb = h->ba[slot], L = bands.nLines[b];
+    double* out = lines + pre_line_index(local, f * PAC_HALF_SHORT + bands.lower[b]);
+    int k = 0;
+    if (env) for (int j = 0; j < b; ++j) k += bands.omitted[j] ? 1 : 0;
+    if (!bb) {
+        if (env) { if (k < 4) h->env[k] = 0.0; }
+        else for (int i = 0; i < L; ++i) out[i * 32] = 0.0;
+        return;
+    }
+    int cap = 1, base = 0, all = 0;                            // workspace offset: power-of-two capacities of the bands before
+    while (cap < L) cap <<= 1;
+    for (int j = 0; j < nB; ++j) {
+        int c = 1;
+        while (c < bands.nLines[j]) c <<= 1;
+        if (j < b) base += c;
+        all += c;
+    }
+    base += f * all;                                           // <= 2 * 1024 in total for either frame type
+    double* wsA = ws + ((size_t)(local >> 5) * (2 * PRE_WS_PER_CB) + (size_t)base) * 32 + (local & 31);
+    double* wsB = wsA + (size_t)PRE_WS_PER_CB * 32;
+    int nBytes;
+    long long bit0;
+    BitR br = rec_reader(a, cbBase + local, &nBytes, &bit0);
+    br.pos = bit0 + h->pos[slot];
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
+    int werr = 0;
+    if (env) {                                                 // one envelope value (coder/codec.py:111-132)
+        double v;
+        thread_dequantize_gain_shape<1>(pt, br, bb, 1, 1, wsA, wsB, &v, &werr);
+        if (k < 4) h->env[k] = v;
+    } else {
+        thread_dequantize_gain_shape<32>(pt, br, bb * L, L, cap, wsA, wsB, out, &werr);
+    }
+    if (werr) atomicOr(a.err, werr);
 }
 
 template <typename T>
 __global__ void __launch_bounds__(DEC_NT, 3)
-k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbPre* __restrict__ preAll, const DNode* __restrict__ nodesG) {
+k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DecSmem S;
     dec_smem_carve(smem_raw, S);
@@ -213,8 +220,7 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbPre* __restrict__ pr
         if (tid == 0) atomicOr(a.err, PVQ_ERR_STACK);
         nBytes = DEC_REC_MAX;
     }
-    const CbPre* pre = preAll ? preAll + blockIdx.x : nullptr;
-    const DNode* region = preAll ? nodesG + (size_t)blockIdx.x * PRE_NODES_PER_CB : nullptr;
+    const CbHdr* pre = preAll ? preAll + blockIdx.x : nullptr;
     const unsigned char* src = a.buf + a.payOff[cb];
     if (!pre) for (int i = tid; i < nBytes; i += DEC_NT) S.rec[i] = src[i];
     for (int i = tid; i < 2048; i += DEC_NT) S.y[i] = 0.0;
@@ -227,11 +233,10 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbPre* __restrict__ pr
     if (nBytes > 0) {
         if (!cur) {
             int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err, pre, region, 0);
+            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err, pre, preLines, blockIdx.x, 0);
         } else {
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err, pre,
-                                            region ? region + sf * PRE_SHORT_NODES : nullptr, sf);
+                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err, pre, preLines, blockIdx.x, sf);
         }
     }
     double* dst = a.frames + cb * 2048;
@@ -345,11 +350,15 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     size_t oPayB = carve((size_t)(nCb + C) * sizeof(int));
     size_t oErr = carve(sizeof(int));
     size_t oFrames = carve((size_t)nCb * 2048 * sizeof(double));
-    // VQ streams: k_parse output for one batch of channel-blocks at a time (reused batch after batch)
-    const bool vq = ctx->cfg.use_vq != 0;
+    // VQ streams: dequantised lines + workspaces for one batch of channel-blocks at a time (reused batch after batch)
+    // (band layouts the batched front end is not sized for fall back to the in-CTA parse of decode_front)
+    const bool vq = ctx->cfg.use_vq != 0 && ctx->host.longBands.nBands <= PRE_SLOTS &&
+                    PAC_SUBFRAMES * ctx->host.shortBands.nBands <= PRE_SLOTS && ctx->host.sbrNOmitted <= 4;
     const long long batchCb = vq ? std::min<long long>(nCb, DEC_BATCH_CB) : 0;
-    size_t oPre = carve((size_t)batchCb * sizeof(CbPre));
-    size_t oNodes = carve((size_t)batchCb * PRE_NODES_PER_CB * sizeof(DNode));
+    const long long batchGroups = (batchCb + 31) / 32;
+    size_t oPre = carve((size_t)batchCb * sizeof(CbHdr));
+    size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));
+    size_t oWs = carve((size_t)batchGroups * 32 * 2 * PRE_WS_PER_CB * sizeof(double));
     void* scr = nullptr;
     if ((rc = pac_scratch(ctx, o, &scr))) return rc;
     unsigned char* sb = (unsigned char*)scr;
@@ -378,11 +387,16 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
         for (long long q0 = 0; q0 < nCbC; q0 += vq ? batchCb : nCbC) {
             const long long nq = vq ? std::min(batchCb, nCbC - q0) : nCbC;
             a.cb0 = cb0 + q0;
-            CbPre* dPre = vq ? (CbPre*)(sb + oPre) : nullptr;
-            DNode* dNodes = vq ? (DNode*)(sb + oNodes) : nullptr;
-            if (vq) k_parse<<<(unsigned)((nq + PARSE_CBS - 1) / PARSE_CBS), PARSE_NT, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre, dNodes);
-            if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dNodes);
-            else k_decode<double><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dNodes);
+            CbHdr* dPre = vq ? (CbHdr*)(sb + oPre) : nullptr;
+            double* dLines = vq ? (double*)(sb + oLines) : nullptr;
+            if (vq) {
+                const int nChunks = (int)((nq + DQ_NT - 1) / DQ_NT);
+                k_hdr<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre);
+                k_dequant<<<(unsigned)(nChunks * PRE_SLOTS), DQ_NT, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, nChunks, dPre, dLines,
+                                                                          (double*)(sb + oWs));
+            }
+            if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
+            else k_decode<double><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
         }
         if (c == 0) { cudaEventRecord(ctx->ev[3], st); ctx->evValid[1] = 1; }
         PAC_CHECK(cudaGetLastError());

@@ -21,21 +21,24 @@ static __device__ unsigned long long g_pac_dphase[32];
 #define DEC_GROUP 32              // lanes per band in the per-band phases (8 / 16 measured slower: divergent groups of a warp serialise)
 #define DEC_MAX_NODES 512         // split-tree nodes per frame (a 128 kb/s long frame has ~150); sized for 3 CTAs per SM
 
-// What k_parse (decode.cu) leaves per channel-block for k_decode: slot = sub-frame * nBands + band.
+// Batched front end of VQ streams (decode.cu): k_hdr reads the frame headers of a channel-block,
+// k_dequant dequantises one band per thread into a lane-interleaved line array, k_decode then only
+// runs SBR + IMDCT.  slot = sub-frame * nBands + band.
 #define PRE_SLOTS 48              // 17 long bands, or 8 sub-frames x 6 short bands
-#define PRE_SHORT_NODES 96        // node capacity of one short sub-frame (a long frame has DEC_MAX_NODES)
-#define PRE_NODES_PER_CB (PAC_SUBFRAMES * PRE_SHORT_NODES)
-struct CbPre {
-    double gain[PRE_SLOTS];           // inv-mu-law gain * L of the band
-    short tail[PRE_SLOTS];            // last node of the band in the frame's list (-1: shape = ones)
+#define PRE_WS_PER_CB 2048        // bound on the sum of the bands' power-of-two capacities (each < 2 nLines)
+struct CbHdr {
+    double env[4];                    // SBR envelope values (k_dequant), in omitted-band order
+    unsigned short pos[PRE_SLOTS];    // payload bit position of the band within the record
     unsigned char ba[PRE_SLOTS];      // bit allocation
-    unsigned short nNodes[PAC_SUBFRAMES];
     unsigned char scale[PAC_SUBFRAMES];
     unsigned char sbr;                // long frame of an SBR stream with coded envelope bands
     unsigned char flags;              // bit 2 last, 1 cur, 0 next transient; bit 7: record present
     unsigned char pad[6];
 };
-static_assert(PRE_NODES_PER_CB >= DEC_MAX_NODES, "node region per channel-block");
+// line k of sub-frame f of channel-block c (index within the batch): 32 blocks interleaved
+__device__ __forceinline__ size_t pre_line_index(long long c, int k) {
+    return ((size_t)(c >> 5) * 1024 + (size_t)k) * 32 + (size_t)(c & 31);
+}
 
 struct DecSmem {
     unsigned char* rec;   // [DEC_REC_MAX] payload bytes
@@ -85,8 +88,8 @@ __device__ __forceinline__
 static __device__ __noinline__
 #endif
 int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long recBits,
-                                                bool isLong, int* err, const CbPre* __restrict__ pre,
-                                                const DNode* __restrict__ preNodes, int sf) {
+                                                bool isLong, int* err, const CbHdr* __restrict__ pre,
+                                                const double* __restrict__ preLines, long long preCb, int sf) {
     DecSmem S;
     dec_smem_carve(raw, S);
     const int H = isLong ? PAC_HALF_LONG : PAC_HALF_SHORT;
@@ -98,38 +101,18 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     //     allocations as fixed-width fields up front: one warp reads them in parallel (lane = band) and
     //     places the band payloads with a scan.  Block-FP interleaves them with the mantissas: thread 0.
     if (pre) {
-        // header and split trees were parsed by k_parse: bring this frame's part into shared memory
-        const int n = min((int)pre->nNodes[sf], isLong ? DEC_MAX_NODES : PRE_SHORT_NODES);
-        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(preNodes);
-        unsigned long long* dst = reinterpret_cast<unsigned long long*>(S.nodes);
-        for (int i = tid; i < n * (int)(sizeof(DNode) / 8); i += DEC_NT) dst[i] = src[i];
-        if (warp == 0) {
-            const bool act = lane < nB;
-            const bool sbr = isLong && pre->sbr;
-            const int slot = sf * nB + lane;
-            int cap = 0;
-            if (act) { cap = 1; while (cap < bands.nLines[lane]) cap <<= 1; }
-            int cinc = cap;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int tc = __shfl_up_sync(0xffffffffu, cinc, o);
-                if (lane >= o) cinc += tc;
-            }
-            if (act) {
-                S.ba[lane] = pre->ba[slot];
-                S.capOff[lane] = cinc - cap;
-                BandDec bd;
-                bd.gain = pre->gain[slot]; bd.tail = pre->tail[slot];
-                bd.L = (sbr && bands.omitted[lane]) ? 1 : bands.nLines[lane];
-                S.bd[lane] = bd;
-            }
-            if (lane == nB - 1) S.capOff[nB] = cinc;
-            if (lane == 0) {
-                S.misc[5] = pre->scale[sf];
-                S.misc[6] = sbr;
-                S.misc[7] = n;
-            }
+        // the bands were dequantised by k_dequant: fetch this frame's lines (still scaled)
+        const bool sbrP = isLong && pre->sbr;
+        const int cut = dev->sbrCutoff;
+        for (int i = tid; i < H; i += DEC_NT)
+            S.lines[i] = (sbrP && i >= cut) ? 0.0 : preLines[pre_line_index(preCb, sf * PAC_HALF_SHORT + i)];
+        if (tid == 0) {
+            S.misc[5] = pre->scale[sf];
+            S.misc[6] = sbrP;
         }
+        __syncthreads();
+        if (sbrP && tid < dev->sbrNOmitted && tid < 4) S.lines[cut + tid] = pre->env[tid];   // coder/codec.py:111-132
+        __syncthreads();
     } else
     if (dev->useVQ) {
         if (warp == 0) {
@@ -210,8 +193,10 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
         S.capOff[nB] = c;
         if (br.pos > recBits) atomicOr(err, PVQ_ERR_STACK);
     }
-    for (int i = tid; i < H; i += DEC_NT) S.lines[i] = 0.0;
-    __syncthreads();
+    if (!pre) {
+        for (int i = tid; i < H; i += DEC_NT) S.lines[i] = 0.0;
+        __syncthreads();
+    }
     const bool sbr = S.misc[6] != 0;
     const int scale = S.misc[5];
     DPHASE(0);
@@ -219,11 +204,12 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
     //     block floating point directly
     PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
     const int omPos = dev->sbrCutoff;
-    if (dev->useVQ) {
+    if (pre) {
+    } else if (dev->useVQ) {
         constexpr int G = DEC_GROUP;
         const int grp = tid / G;
         // phase A is scalar: one THREAD per band, bands dealt round-robin to the warps (<= 4 per warp)
-        if (!pre) {
+        {
             const int b = lane * (DEC_NT / 32) + warp;
             const int bb = b < nB ? S.ba[b] : 0;
             if (bb) {
@@ -313,12 +299,12 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
 // adds its windowed IMDCT into y[yOff .. yOff+N).
 template <int N, typename T>
 __device__ void decode_frame(const PacDev* __restrict__ dev, const DecSmem& S, long long recBits, int shape, int yOff,
-                             int* err, const CbPre* __restrict__ pre = nullptr, const DNode* __restrict__ preNodes = nullptr,
-                             int sf = 0) {
+                             int* err, const CbHdr* __restrict__ pre = nullptr, const double* __restrict__ preLines = nullptr,
+                             long long preCb = 0, int sf = 0) {
     constexpr int Q = N / 4;
     const int tid = threadIdx.x;
     const bool isLong = N == PAC_NLONG;
-    const int scale = decode_front(dev, S.raw, recBits, isLong, err, pre, preNodes, sf);
+    const int scale = decode_front(dev, S.raw, recBits, isLong, err, pre, preLines, preCb, sf);
     // (4) undo the overall scale, IMDCT, synthesis window (coder/codec.py:85-89)
     // T = float: the transform runs in fp32 (fast path; PCM within 1 LSB of the fp64 result).
     const PacTables<T>& t = psy_tabs<T>(dev);

@@ -13,6 +13,7 @@
 // at A(j) = N(l,k) - N(l,k-j) - N(l-1,k-j) (the number of vectors with |x_i| < j), so j is found by
 // bisection instead of the reference's linear scan.  Serial; run by ONE thread.  x[0..L) receives
 // the signed pulse counts as doubles.
+template <int XS = 1>   // XS: element stride of x (the batched dequantiser interleaves 32 lanes)
 __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b, int L, long long K, double* x,
                                            int* err) {
     long long k = K;
@@ -32,7 +33,7 @@ __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b
                 if (pvq_N(t, mid, k) > r) hi = mid; else lo = mid + 1;
             }
             const int stop = L - lo;                      // first position whose remaining length is lo
-            for (; i < stop; ++i) x[i] = 0.0;
+            for (; i < stop; ++i) x[i * XS] = 0.0;
             --i;
             continue;
         }
@@ -48,13 +49,13 @@ __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b
         bool neg = false;
         if (r >= nj) { neg = true; r -= nj; }
         if (r >= nj) { *err |= PVQ_ERR_DEGENERATE; r = 0ull; }    // index outside the codebook
-        x[i] = neg ? -(double)lo : (double)lo;
+        x[i * XS] = neg ? -(double)lo : (double)lo;
         k -= lo;
     }
-    for (; i < L; ++i) x[i] = 0.0;
+    for (; i < L; ++i) x[i * XS] = 0.0;
     if (k > 0) {
         if (r != 0ull) *err |= PVQ_ERR_DEGENERATE;
-        x[L - 1] = (double)k;
+        x[(L - 1) * XS] = (double)k;
     }
 }
 
@@ -270,60 +271,89 @@ __device__ __forceinline__ void grp_parse_gain_shape(const PvqTab& t, BitR& br, 
     }
 }
 
-// Phase A as its own kernel (k_parse, decode.cu): ONE THREAD per band, the 32 lanes of a warp hold
-// the same band of 32 different channel-blocks, so the lanes run the same loop with similar trip
-// counts and thousands of these serial chains are in flight per SM.  Nodes go to the frame's list in
-// global memory (slots from a shared-memory counter); children without bits are flagged on the
-// parent (DN_ZMID / DN_ZSIDE) instead of zeroed, because the workspaces do not exist yet.
-__device__ __forceinline__ void thread_parse_band(const PvqTab& t, BitR& br, int R, int L, int base, int cap,
-                                                  DNode* __restrict__ nodes, int* nNodes, int maxNodes, double* gainOut,
-                                                  short* tailOut, int* err) {
-    int bg, bs, tail = -1;
+// dequantize_gain_shape for one band in ONE THREAD (k_dequant, decode.cu): the 32 lanes of a warp
+// hold the same band of 32 different channel-blocks, so they run the same loops with similar trip
+// counts, nothing waits at a barrier, and thousands of these serial chains (field widths depend on
+// the angles just read; the index decode is sequential by nature) are in flight per SM.  Same tree
+// walk as warp_dequantize_gain_shape above.  wsA / wsB / out: per-lane arrays with element stride XS
+// (lane-interleaved global memory: every access of a converged warp is one coalesced line).
+struct TDecNode { short off, cap, n; unsigned char buf, state, root, z; int bits, entry; double theta; };
+template <int XS>
+__device__ __forceinline__ void thread_normalise(double* v, int n) {
+    double ss = 0.0;
+    for (int i = 0; i < n; ++i) { const double c = v[i * XS]; ss += c * c; }
+    const double nr = sqrt(ss);
+    if (nr != 0.0)
+        for (int i = 0; i < n; ++i) v[i * XS] = v[i * XS] / nr;
+}
+template <int XS>
+__device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, BitR& br, int R, int L, int cap,
+                                                             double* wsA, double* wsB, double* out, int* err) {
+    int bg, bs;
     gs_alloc(t, R, L, &bg, &bs);
+    bool ones = true;
     if (bs != 0) {
-        ParseNode st[24];
+        ones = false;
+        TDecNode st[24];
         int sp = 0, used = 0;
-        st[sp++] = {(short)base, (short)cap, (short)L, 0, bs, 1};
+        st[sp++] = {0, (short)cap, (short)L, 0, 0, 1, 0, bs, -1, 0.0};
         while (sp > 0) {
-            const ParseNode nd = st[--sp];
-            DNode dn;
-            dn.off = nd.off; dn.n = nd.n; dn.prev = (short)tail;
-            dn.capLog2 = (unsigned char)(31 - __clz((int)nd.cap));
-            dn.flags = (unsigned char)((nd.buf ? DN_BUF : 0) | (nd.root ? DN_ROOT : 0));
-            int aMid = 0, aSide = 0;
-            const bool leaf = nd.bits <= PVQ_SPLIT_BITS;
-            if (leaf) {
+            const TDecNode nd = st[sp - 1];
+            double* cur = (nd.buf ? wsB : wsA) + nd.off * XS;
+            double* oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+            if (nd.bits <= PVQ_SPLIT_BITS) {              // leaf
                 long long K;
                 int w;
                 pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
-                dn.u = br_get(br, w);
-                dn.K = (int)K;
-                dn.flags |= DN_LEAF;
+                const unsigned long long idx = br_get(br, w);
                 used += w;
-            } else {
-                const int half = (nd.n + 1) / 2;
-                int aT, aMs;
+                pvq_vector<XS>(t, idx, nd.n, K, cur, err);
+                thread_normalise<XS>(cur, nd.n);
+                if (nd.root) thread_normalise<XS>(cur, nd.n);   // a root leaf is normalised twice (:214-218)
+                --sp;
+                continue;
+            }
+            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+            if (nd.state == 0) {                          // first visit: theta, then children
+                int aT, aMs, aMid, aSide, entry;
                 gs_alloc(t, nd.bits, half, &aT, &aMs);
                 if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
                 const unsigned long long ti = br_get(br, aT);
                 used += aT;
                 double theta, l2t;
-                int entry;
                 theta_terms(t, ti, aT, &theta, &l2t, &entry);
                 ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
-                dn.u = (unsigned long long)__double_as_longlong(theta);
-                dn.K = entry;
-                dn.flags |= (unsigned char)((aMid <= 0 ? DN_ZMID : 0) | (aSide <= 0 ? DN_ZSIDE : 0));
+                st[sp - 1].theta = theta;
+                st[sp - 1].entry = entry;
+                st[sp - 1].state = 1;
+                st[sp - 1].z = (unsigned char)((aMid <= 0 ? 1 : 0) | (aSide <= 0 ? 2 : 0));   // children without bits read as zeros
+                if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; ones = true; break; }
+                if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (unsigned char)(1 - nd.buf), 0, 0, 0, aSide, -1, 0.0};
+                if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (unsigned char)(1 - nd.buf), 0, 0, 0, aMid, -1, 0.0};
+                continue;
             }
-            const int slot = atomicAdd(nNodes, 1);
-            if (slot >= maxNodes) { *err |= PVQ_ERR_STACK; tail = -1; break; }
-            nodes[slot] = dn;
-            tail = slot;
-            if (leaf) continue;
-            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
-            const int half = (nd.n + 1) / 2, hc = nd.cap / 2;
-            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, 0};
-            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid, 0};
+            // children done: recombine (coder/gain_shape_quantize.py:449-463)
+            double ct, sn;
+            if (nd.entry >= 0) {
+                ct = t.theta[4 * nd.entry + 2];
+                sn = t.theta[4 * nd.entry + 3];
+            } else {
+                pm_sincos(nd.theta, &sn, &ct);
+            }
+            const double r2 = sqrt(2.0);
+            double ss = 0.0;
+            for (int i = 0; i < half; ++i) {
+                const double m = (nd.z & 1) ? 0.0 : oth[i * XS], s = (nd.z & 2) ? 0.0 : oth[(hc + i) * XS];
+                const double l = (m * ct + s * sn) / r2;
+                const double r = (m * ct - s * sn) / r2;
+                if (i < mid) { cur[i * XS] = l; ss += l * l; }     // odd n: the padded last element of left is dropped
+                cur[(mid + i) * XS] = r;
+                ss += r * r;
+            }
+            const double nr = sqrt(ss);
+            if (nr != 0.0)
+                for (int i = 0; i < n; ++i) cur[i * XS] = cur[i * XS] / nr;
+            --sp;
         }
         bg += bs - used;
     }
@@ -332,8 +362,8 @@ __device__ __forceinline__ void thread_parse_band(const PvqTab& t, BitR& br, int
     const unsigned long long gi = br_get(br, bg);
     const double gq = dequantize_uniform(gi, bg);
     const double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
-    *gainOut = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
-    *tailOut = (short)tail;
+    const double gain = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
+    for (int i = 0; i < L; ++i) out[i * XS] = ones ? gain : gain * wsA[i * XS];
 }
 
 // Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...
