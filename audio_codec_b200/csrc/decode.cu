@@ -109,7 +109,8 @@ __device__ __forceinline__ BitR rec_reader(const DecArgs& a, long long cb, int* 
 // k_hdr: one thread per channel-block reads the block flags and every frame header (overall scale,
 // bit allocations) and places the band payloads (coder/pacfile.py:177-229).
 __global__ void __launch_bounds__(128)
-k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHdr* __restrict__ hdrs) {
+k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHdr* __restrict__ hdrs,
+      int* __restrict__ perm, int* __restrict__ counts) {
     const int local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= nCb) return;
     int nBytes;
@@ -149,6 +150,12 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
     }
     h->sbr = sbrF;
     h->flags = fl;
+    // dense order for k_dequant: its warps then hold 32 blocks of the same kind (17 long bands against
+    // 48 short slots); blocks without a record take no position
+    int p = -1;
+    if (fl & 0x80u) p = ((fl >> 1) & 1) ? nCb - 1 - atomicAdd(&counts[1], 1) : atomicAdd(&counts[0], 1);
+    h->p = p;
+    if (p >= 0) perm[p] = local;
 }
 
 // k_dequant: one thread per (channel-block, band).  A CTA holds one band slot of DQ_NT consecutive
@@ -158,10 +165,14 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
 #define DQ_NT 128
 __global__ void __launch_bounds__(DQ_NT)
 k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, int nChunks, CbHdr* __restrict__ hdrs,
-          double* __restrict__ lines, double* __restrict__ ws) {
+          double* __restrict__ lines, double* __restrict__ ws, const int* __restrict__ perm,
+          const int* __restrict__ counts) {
     const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
-    const int local = chunk * DQ_NT + threadIdx.x;
-    if (local >= nCb) return;
+    const int pos = chunk * DQ_NT + threadIdx.x;
+    const int nLong = counts[0], nShort = counts[1];
+    if (pos >= nCb || (pos >= nLong && pos < nCb - nShort)) return;
+    if (q >= dev->longBands.nBands && pos < nLong) return;
+    const int local = perm[pos];
     CbHdr* h = hdrs + local;
     const unsigned char fl = h->flags;
     if (!(fl & 0x80u)) return;
@@ -172,7 +183,7 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
     const int f = q / nB, b = nB - 1 - (q - f * nB), slot = f * nB + b;
     const bool sbr = h->sbr != 0, env = sbr && bands.omitted[b];
     const int bb = h->ba[slot], L = bands.nLines[b];
-    double* out = lines + pre_line_index(local, f * PAC_HALF_SHORT + bands.lower[b]);
+    double* out = lines + pre_line_index(pos, f * PAC_HALF_SHORT + bands.lower[b]);
     int k = 0;
     if (env) for (int j = 0; j < b; ++j) k += bands.omitted[j] ? 1 : 0;
     if (!bb) {
@@ -189,7 +200,7 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
         all += c;
     }
     base += f * all;                                           // <= 2 * 1024 in total for either frame type
-    double* wsA = ws + ((size_t)(local >> 5) * (2 * PRE_WS_PER_CB) + (size_t)base) * 32 + (local & 31);
+    double* wsA = ws + ((size_t)(pos >> 5) * (2 * PRE_WS_PER_CB) + (size_t)base) * 32 + (pos & 31);
     double* wsB = wsA + (size_t)PRE_WS_PER_CB * 32;
     int nBytes;
     long long bit0;
@@ -359,6 +370,7 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     size_t oPre = carve((size_t)batchCb * sizeof(CbHdr));
     size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));
     size_t oWs = carve((size_t)batchGroups * 32 * 2 * PRE_WS_PER_CB * sizeof(double));
+    size_t oPerm = carve((size_t)(batchCb + 2) * sizeof(int));
     void* scr = nullptr;
     if ((rc = pac_scratch(ctx, o, &scr))) return rc;
     unsigned char* sb = (unsigned char*)scr;
@@ -391,9 +403,12 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
             double* dLines = vq ? (double*)(sb + oLines) : nullptr;
             if (vq) {
                 const int nChunks = (int)((nq + DQ_NT - 1) / DQ_NT);
-                k_hdr<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre);
+                int* dPerm = (int*)(sb + oPerm);
+                int* dCounts = dPerm + batchCb;
+                PAC_CHECK(cudaMemsetAsync(dCounts, 0, 2 * sizeof(int), st));
+                k_hdr<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre, dPerm, dCounts);
                 k_dequant<<<(unsigned)(nChunks * PRE_SLOTS), DQ_NT, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, nChunks, dPre, dLines,
-                                                                          (double*)(sb + oWs));
+                                                                          (double*)(sb + oWs), dPerm, dCounts);
             }
             if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
             else k_decode<double><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);

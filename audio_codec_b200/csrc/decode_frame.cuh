@@ -33,7 +33,8 @@ struct CbHdr {
     unsigned char scale[PAC_SUBFRAMES];
     unsigned char sbr;                // long frame of an SBR stream with coded envelope bands
     unsigned char flags;              // bit 2 last, 1 cur, 0 next transient; bit 7: record present
-    unsigned char pad[6];
+    unsigned char pad[2];
+    int p;                            // position in the batch's dense order (long blocks from the front, transient from the back)
 };
 // line k of sub-frame f of channel-block c (index within the batch): 32 blocks interleaved
 __device__ __forceinline__ size_t pre_line_index(long long c, int k) {
@@ -105,7 +106,7 @@ int decode_front(const PacDev* __restrict__ dev, unsigned char* raw, long long r
         const bool sbrP = isLong && pre->sbr;
         const int cut = dev->sbrCutoff;
         for (int i = tid; i < H; i += DEC_NT)
-            S.lines[i] = (sbrP && i >= cut) ? 0.0 : preLines[pre_line_index(preCb, sf * PAC_HALF_SHORT + i)];
+            S.lines[i] = (sbrP && i >= cut) ? 0.0 : preLines[pre_line_index(pre->p, sf * PAC_HALF_SHORT + i)];
         if (tid == 0) {
             S.misc[5] = pre->scale[sf];
             S.misc[6] = sbrP;
