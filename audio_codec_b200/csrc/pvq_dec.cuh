@@ -14,8 +14,9 @@
 // bisection instead of the reference's linear scan.  Serial; run by ONE thread.  x[0..L) receives
 // the signed pulse counts as doubles.
 template <int XS = 1>   // XS: element stride of x (the batched dequantiser interleaves 32 lanes)
-__device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b, int L, long long K, double* x,
-                                           int* err) {
+__device__ __forceinline__ double pvq_vector(const PvqTab& t, unsigned long long b, int L, long long K, double* x,
+                                             int* err) {
+    double ss = 0.0;                                      // sum of squares in index order (zeros add nothing)
     long long k = K;
     unsigned long long r = b;
     int i = 0;
@@ -49,14 +50,18 @@ __device__ __forceinline__ void pvq_vector(const PvqTab& t, unsigned long long b
         bool neg = false;
         if (r >= nj) { neg = true; r -= nj; }
         if (r >= nj) { *err |= PVQ_ERR_DEGENERATE; r = 0ull; }    // index outside the codebook
-        x[i * XS] = neg ? -(double)lo : (double)lo;
+        const double xv = neg ? -(double)lo : (double)lo;
+        x[i * XS] = xv;
+        ss += xv * xv;
         k -= lo;
     }
     for (; i < L; ++i) x[i * XS] = 0.0;
     if (k > 0) {
         if (r != 0ull) *err |= PVQ_ERR_DEGENERATE;
         x[(L - 1) * XS] = (double)k;
+        ss += (double)k * (double)k;
     }
+    return ss;
 }
 
 struct DecNode { short off, cap, n, buf; int bits; double theta; short state, root; };
@@ -277,83 +282,95 @@ __device__ __forceinline__ void grp_parse_gain_shape(const PvqTab& t, BitR& br, 
 // the angles just read; the index decode is sequential by nature) are in flight per SM.  Same tree
 // walk as warp_dequantize_gain_shape above.  wsA / wsB / out: per-lane arrays with element stride XS
 // (lane-interleaved global memory: every access of a converged warp is one coalesced line).
-struct TDecNode { short off, cap, n; unsigned char buf, state, root, z; int bits, entry; double theta; };
-template <int XS>
-__device__ __forceinline__ void thread_normalise(double* v, int n) {
-    double ss = 0.0;
-    for (int i = 0; i < n; ++i) { const double c = v[i * XS]; ss += c * c; }
-    const double nr = sqrt(ss);
-    if (nr != 0.0)
-        for (int i = 0; i < n; ++i) v[i * XS] = v[i * XS] / nr;
-}
+// A node leaves its vector UN-normalised in the workspace and hands its norm to the parent, which
+// divides as it reads (the same operations on the same values as normalise-then-read, one load and one
+// store pass fewer per node).
+struct TDecNode { short off, cap, n, par; unsigned char buf, state, root, z; int bits, entry; double theta, nrMid, nrSide; };
+static __device__ __noinline__ void pm_sincos_pair(double x, double* s, double* c) { sincos(x, s, c); }
 template <int XS>
 __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, BitR& br, int R, int L, int cap,
-                                                             double* wsA, double* wsB, double* out, int* err) {
+                                                             double* wsA, double* wsB, double* __restrict__ out, int* err) {
     int bg, bs;
     gs_alloc(t, R, L, &bg, &bs);
     bool ones = true;
+    double rootNr = 0.0;
     if (bs != 0) {
         ones = false;
         TDecNode st[24];
         int sp = 0, used = 0;
-        st[sp++] = {0, (short)cap, (short)L, 0, 0, 1, 0, bs, -1, 0.0};
+        st[sp++] = {0, (short)cap, (short)L, -1, 0, 0, 1, 0, bs, -1, 0.0, 0.0, 0.0};
         while (sp > 0) {
             const TDecNode nd = st[sp - 1];
-            double* cur = (nd.buf ? wsB : wsA) + nd.off * XS;
-            double* oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+            double* __restrict__ cur = (nd.buf ? wsB : wsA) + nd.off * XS;
+            const double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+            double nrOut;
             if (nd.bits <= PVQ_SPLIT_BITS) {              // leaf
                 long long K;
                 int w;
                 pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
                 const unsigned long long idx = br_get(br, w);
                 used += w;
-                pvq_vector<XS>(t, idx, nd.n, K, cur, err);
-                thread_normalise<XS>(cur, nd.n);
-                if (nd.root) thread_normalise<XS>(cur, nd.n);   // a root leaf is normalised twice (:214-218)
-                --sp;
-                continue;
-            }
-            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
-            if (nd.state == 0) {                          // first visit: theta, then children
-                int aT, aMs, aMid, aSide, entry;
-                gs_alloc(t, nd.bits, half, &aT, &aMs);
-                if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
-                const unsigned long long ti = br_get(br, aT);
-                used += aT;
-                double theta, l2t;
-                theta_terms(t, ti, aT, &theta, &l2t, &entry);
-                ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
-                st[sp - 1].theta = theta;
-                st[sp - 1].entry = entry;
-                st[sp - 1].state = 1;
-                st[sp - 1].z = (unsigned char)((aMid <= 0 ? 1 : 0) | (aSide <= 0 ? 2 : 0));   // children without bits read as zeros
-                if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; ones = true; break; }
-                if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (unsigned char)(1 - nd.buf), 0, 0, 0, aSide, -1, 0.0};
-                if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (unsigned char)(1 - nd.buf), 0, 0, 0, aMid, -1, 0.0};
-                continue;
-            }
-            // children done: recombine (coder/gain_shape_quantize.py:449-463)
-            double ct, sn;
-            if (nd.entry >= 0) {
-                ct = t.theta[4 * nd.entry + 2];
-                sn = t.theta[4 * nd.entry + 3];
+                nrOut = sqrt(pvq_vector<XS>(t, idx, nd.n, K, cur, err));
+                if (nd.root) {                            // a root leaf is normalised twice (:214-218)
+                    double ss = 0.0;
+                    for (int i = 0; i < nd.n; ++i) {
+                        const double c = nrOut != 0.0 ? cur[i * XS] / nrOut : cur[i * XS];
+                        cur[i * XS] = c;
+                        ss += c * c;
+                    }
+                    nrOut = sqrt(ss);
+                }
             } else {
-                pm_sincos(nd.theta, &sn, &ct);
+                const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+                if (nd.state == 0) {                      // first visit: theta, then children
+                    int aT, aMs, aMid, aSide, entry;
+                    gs_alloc(t, nd.bits, half, &aT, &aMs);
+                    if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+                    const unsigned long long ti = br_get(br, aT);
+                    used += aT;
+                    double theta, l2t;
+                    theta_terms(t, ti, aT, &theta, &l2t, &entry);
+                    ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
+                    st[sp - 1].theta = theta;
+                    st[sp - 1].entry = entry;
+                    st[sp - 1].state = 1;
+                    st[sp - 1].z = (unsigned char)((aMid <= 0 ? 1 : 0) | (aSide <= 0 ? 2 : 0));   // children without bits read as zeros
+                    if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; ones = true; break; }
+                    const short par = (short)(sp - 1);
+                    if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, par, (unsigned char)(1 - nd.buf), 0, 0, 0, aSide, -1, 0.0, 0.0, 0.0};
+                    if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, par, (unsigned char)(1 - nd.buf), 0, 0, 0, aMid, -1, 0.0, 0.0, 0.0};
+                    continue;
+                }
+                // children done: recombine (coder/gain_shape_quantize.py:449-463)
+                double ct, sn;
+                if (nd.entry >= 0) {
+                    ct = t.theta[4 * nd.entry + 2];
+                    sn = t.theta[4 * nd.entry + 3];
+                } else {
+                    pm_sincos_pair(nd.theta, &sn, &ct);
+                }
+                const double r2 = sqrt(2.0), nm = nd.nrMid, ns = nd.nrSide;
+                const bool zm = nd.z & 1, zs = nd.z & 2;
+                double ss = 0.0;
+#pragma unroll 4
+                for (int i = 0; i < half; ++i) {
+                    double m = zm ? 0.0 : oth[i * XS], s = zs ? 0.0 : oth[(hc + i) * XS];
+                    if (nm != 0.0) m = m / nm;
+                    if (ns != 0.0) s = s / ns;
+                    const double l = (m * ct + s * sn) / r2;
+                    const double r = (m * ct - s * sn) / r2;
+                    if (i < mid) { cur[i * XS] = l; ss += l * l; }     // odd n: the padded last element of left is dropped
+                    cur[(mid + i) * XS] = r;
+                    ss += r * r;
+                }
+                nrOut = sqrt(ss);
             }
-            const double r2 = sqrt(2.0);
-            double ss = 0.0;
-            for (int i = 0; i < half; ++i) {
-                const double m = (nd.z & 1) ? 0.0 : oth[i * XS], s = (nd.z & 2) ? 0.0 : oth[(hc + i) * XS];
-                const double l = (m * ct + s * sn) / r2;
-                const double r = (m * ct - s * sn) / r2;
-                if (i < mid) { cur[i * XS] = l; ss += l * l; }     // odd n: the padded last element of left is dropped
-                cur[(mid + i) * XS] = r;
-                ss += r * r;
+            --sp;                                          // hand the norm to the parent (mid child: same offset)
+            if (nd.par >= 0) {
+                if (nd.off == st[nd.par].off) st[nd.par].nrMid = nrOut; else st[nd.par].nrSide = nrOut;
+            } else {
+                rootNr = nrOut;
             }
-            const double nr = sqrt(ss);
-            if (nr != 0.0)
-                for (int i = 0; i < n; ++i) cur[i * XS] = cur[i * XS] / nr;
-            --sp;
         }
         bg += bs - used;
     }
@@ -363,7 +380,13 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
     const double gq = dequantize_uniform(gi, bg);
     const double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
     const double gain = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
-    for (int i = 0; i < L; ++i) out[i * XS] = ones ? gain : gain * wsA[i * XS];
+    const double* __restrict__ shape = wsA;
+#pragma unroll 4
+    for (int i = 0; i < L; ++i) {
+        double v = 1.0;
+        if (!ones) { v = shape[i * XS]; if (rootNr != 0.0) v = v / rootNr; }
+        out[i * XS] = ones ? gain : gain * v;
+    }
 }
 
 // Phase B: every thread of the CTA takes leaves tid, tid + nThreads, ...
