@@ -14,7 +14,9 @@
 // whole block.  It produces nb[s]+2 written blocks: 0..nb-1, the last block AGAIN
 // (pacfile.py:725-743), then Close()'s zero block (pacfile.py:612-625).
 #include <cub/device/device_scan.cuh>
+#include <algorithm>
 #include "encode_frame.cuh"
+#define ENC_BATCH_CB 32768       // channel-blocks per k_encode / k_pvq / k_pack round (bounds the scratch: ~52 KB each)
 #include "pac_api.h"
 
 // ---------------------------------------------------------------- transient detector
@@ -96,6 +98,12 @@ struct EncArgs {
     int* recBytes;         // [nChBlocks] declared byte size
     unsigned char* zeroSub;// [nChBlocks] 1 if a short sub-frame of this channel is all zero
     int* err;              // [1] OR of soft error flags
+    // batched VQ back end (nullptr: everything in k_encode)
+    EncPre* pre;           // [nBatch]
+    double* preLines;      // [nBatch / 32][1024][32]
+    int* perm;             // [nBatch] dense position -> block of the batch
+    int* counts;           // [2] long / transient blocks placed so far
+    int cb0, nBatch;
 };
 
 template <typename T>
@@ -108,7 +116,7 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
 
     const int tid = threadIdx.x;
     const int C = dev->nChannels;
-    const int cb = blockIdx.x;                // written channel-block index
+    const int cb = blockIdx.x + a.cb0;        // written channel-block index
     const int wb = cb / C, c = cb - wb * C;   // written block (global), channel
     int lo = 0, hi = a.nStreams;
     while (hi - lo > 1) {
@@ -137,6 +145,11 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
         S.misc[4] = 0;
     }
     __syncthreads();
+    if (tid == 0 && a.pre) {                  // dense order for k_pvq: its warps hold blocks of one kind
+        const int p = cur ? a.nBatch - 1 - atomicAdd(&a.counts[1], 1) : atomicAdd(&a.counts[0], 1);
+        a.perm[p] = blockIdx.x;
+        S.misc[8] = p;
+    }
     if (tid == 0) {                           // 3 flag bits (coder/pacfile.py:575-577)
         BitW bw = {S.blockbuf, 0};
         bw_put(bw, last, 1);
@@ -146,9 +159,11 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     }
     __syncthreads();
     int declared = 4;                         // "+4 for block switching" (pacfile.py:560)
+    EncPreOut po = {nullptr, nullptr, 0};
+    if (a.pre) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); }
     if (!cur) {
         int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-        declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err);
+        declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err, po);
     } else {
         // zero sub-frame check (coder/pacfile.py:503-506): the block is dropped if ANY channel has one
         for (int sf = 0; sf < PAC_SUBFRAMES; ++sf) {
@@ -156,11 +171,21 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
             for (int i = tid; i < PAC_NSHORT; i += ENC_NT) nz |= xs[448 + 128 * sf + i] != (T)0;
             if (!__syncthreads_or(nz) && tid == 0) S.misc[4] = 1;
         }
-        for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
+        for (int sf = 0; sf < PAC_SUBFRAMES; ++sf) {
+            po.sf = sf;
             declared += encode_frame<PAC_NSHORT, T>(dev, S, xs + 448 + 128 * sf, PAC_WIN_SINE, true, last || nxt, false,
-                                                 &S.misc[3], a.err);
+                                                 &S.misc[3], a.err, po);
+        }
     }
     __syncthreads();
+    if (a.pre) {                              // the record is assembled by k_pack
+        if (tid == 0) {
+            po.hdr->flags = (unsigned char)((last ? 4 : 0) | (cur ? 2 : 0) | (nxt ? 1 : 0));
+            po.hdr->zeroSub = (unsigned char)S.misc[4];
+            po.hdr->p = S.misc[8];
+        }
+        return;
+    }
     const int nBytes = (declared + 7) / 8;
     unsigned* out = reinterpret_cast<unsigned*>(a.rec + (long long)cb * REC_STRIDE);
     const int nW = min(REC_WORDS, (nBytes + 3) / 4);
@@ -169,6 +194,127 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
         a.recBytes[cb] = nBytes;
         a.zeroSub[cb] = (unsigned char)S.misc[4];
         if (nBytes > REC_STRIDE || S.misc[3] > declared) atomicOr(a.err, PVQ_ERR_STACK);
+    }
+}
+
+// ---------------------------------------------------------------- batched VQ back end
+// k_pvq: one thread per (channel-block, band).  A CTA holds one band slot of PQ_NT consecutive blocks
+// of the dense order; CTAs are ordered widest band first.  Slot q of a long block is band nB-1-q; of
+// a transient block, sub-frame q / 6, band 5 - q % 6.
+#define PQ_NT 128
+__device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, int b, int* base, int* cap, int* wbase) {
+    int c0 = 1, bs = 0, all = 0, wb = 0, wall = 0;
+    while (c0 < bands.nLines[b]) c0 <<= 1;
+    for (int j = 0; j < bands.nBands; ++j) {
+        int c = 1;
+        while (c < bands.nLines[j]) c <<= 1;
+        const int w = bands.nLines[j] / 2 + 3;
+        if (j < b) { bs += c; wb += w; }
+        all += c; wall += w;
+    }
+    *base = bs + f * all;
+    *cap = c0;
+    *wbase = wb + f * wall;
+}
+__global__ void __launch_bounds__(PQ_NT)
+k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict__ ws, int* __restrict__ yws,
+      unsigned* __restrict__ words) {
+    const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
+    const int pos = chunk * PQ_NT + threadIdx.x;
+    const int nLong = a.counts[0], nShort = a.counts[1];
+    if (pos >= a.nBatch || (pos >= nLong && pos < a.nBatch - nShort)) return;
+    if (q >= dev->longBands.nBands && pos < nLong) return;
+    EncPre* h = a.pre + a.perm[pos];
+    const bool cur = (h->flags >> 1) & 1;
+    const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+    const int nB = bands.nBands;
+    if (q >= (cur ? PAC_SUBFRAMES * nB : nB)) return;
+    const int f = q / nB, b = nB - 1 - (q - f * nB), slot = f * nB + b;
+    const int bb = h->ba[slot];
+    if (!bb) { h->used[slot] = 0; return; }
+    const bool env = !cur && dev->useSBR && bands.omitted[b];
+    const int nl = bands.nLines[b], L = env ? 1 : nl, R = env ? bb : bb * nl;
+    int base, cap, wbase;
+    epre_band_layout(bands, f, b, &base, &cap, &wbase);
+    int k = 0;
+    if (env) for (int j = 0; j < b; ++j) k += bands.omitted[j] ? 1 : 0;
+    const size_t grp = (size_t)(pos >> 5), ln = (size_t)(pos & 31);
+    const double* x = a.preLines + epre_line_index(pos, f * PAC_HALF_SHORT + bands.lower[b]);
+    double* wsA = ws + (grp * (2 * EPRE_WS_PER_CB) + (size_t)base) * 32 + ln;
+    double* wsB = wsA + (size_t)EPRE_WS_PER_CB * 32;
+    int* y = yws + (grp * EPRE_WS_PER_CB + (size_t)base) * 32 + ln;
+    unsigned* w = words + (grp * EPRE_WORDS_PER_CB + (size_t)wbase) * 32 + ln;
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
+    int werr = 0;
+    const int used = thread_quantize_gain_shape<32>(pt, x, env, (env && k < 4) ? h->env[k] : 0.0, L, R, wsA, wsB, y, cap, w,
+                                                    nl / 2 + 3, &werr);
+    if (werr) atomicOr(a.err, werr);
+    h->used[slot] = (unsigned short)used;
+    if (used == 0) h->ba[slot] = 0;                       // coder/codec.py:352-353
+}
+
+// k_pack: one warp per channel-block assembles the record (coder/pacfile.py:363-402, :550-608):
+// 3 flag bits, then per frame the overall scale, the bit allocations and the band payloads.
+#define PK_WARPS 4
+__global__ void __launch_bounds__(PK_WARPS * 32)
+k_pack(const PacDev* __restrict__ dev, EncArgs a, const unsigned* __restrict__ words) {
+    __shared__ unsigned s_buf[PK_WARPS][REC_WORDS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int local = blockIdx.x * PK_WARPS + warp;
+    if (local >= a.nBatch) return;
+    unsigned* buf = s_buf[warp];
+    for (int i = lane; i < REC_WORDS; i += 32) buf[i] = 0u;
+    __syncwarp();
+    const EncPre* h = a.pre + local;
+    const int pos = h->p;
+    const bool cur = (h->flags >> 1) & 1;
+    const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+    const int nB = bands.nBands, nF = cur ? PAC_SUBFRAMES : 1, nS = dev->nScaleBits, nM = dev->nMantSizeBits;
+    const bool sbr = !cur && dev->useSBR;
+    if (lane == 0) bw_put_at(buf, 0, (unsigned long long)(h->flags & 7), 3);
+    int p0 = 3, declared = 4;                              // "+4 for block switching" (pacfile.py:560)
+    const unsigned* wcol = words + ((size_t)(pos >> 5) * EPRE_WORDS_PER_CB) * 32 + (pos & 31);
+    for (int f = 0; f < nF; ++f) {
+        const bool act = lane < nB;
+        const int slot = f * nB + lane;
+        const int bab = act ? h->ba[slot] : 0;
+        const int u = bab ? h->used[slot] : 0;
+        int inc = u;
+        int decl = act ? nM + nS + (bab ? ((sbr && bands.omitted[lane]) ? bab : bab * bands.nLines[lane]) : 0) : 0;   // getNumBytesNeeded
+        int wofs = act ? bands.nLines[lane] / 2 + 3 : 0, winc = wofs;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o), tw = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) { inc += t; winc += tw; }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) decl += __shfl_xor_sync(0xffffffffu, decl, o);
+        const int wall = __shfl_sync(0xffffffffu, winc, 31);
+        const int base = p0 + nS + nB * nM;
+        const int mine = base + inc - u, wmine = f * wall + winc - wofs;
+        if (lane == 0) bw_put_at(buf, p0, (unsigned long long)h->scale[f], nS);
+        if (act) bw_put_at(buf, p0 + nS + lane * nM, (unsigned long long)(bab ? bab - 1 : 0), nM);
+        for (int b = 0; b < nB; ++b) {                     // merge the band payloads (disjoint bit ranges)
+            const int ub = __shfl_sync(0xffffffffu, u, b), mb = __shfl_sync(0xffffffffu, mine, b);
+            const int wb = __shfl_sync(0xffffffffu, wmine, b);
+            for (int i = lane; i * 32 < ub; i += 32) {
+                const int nb = min(32, ub - i * 32);
+                bw_put_at(buf, mb + i * 32, (unsigned long long)(wcol[(size_t)(wb + i) * 32] >> (32 - nb)), nb);
+            }
+        }
+        p0 = base + __shfl_sync(0xffffffffu, inc, 31);
+        declared += nS + decl;
+    }
+    __syncwarp();
+    const long long cb = (long long)a.cb0 + local;
+    const int nBytes = (declared + 7) / 8;
+    unsigned* out = reinterpret_cast<unsigned*>(a.rec + cb * REC_STRIDE);
+    const int nW = min(REC_WORDS, (nBytes + 3) / 4);
+    for (int i = lane; i < nW; i += 32) out[i] = __byte_perm(buf[i], 0, 0x0123);
+    if (lane == 0) {
+        a.recBytes[cb] = nBytes;
+        a.zeroSub[cb] = h->zeroSub;
+        if (nBytes > REC_STRIDE || p0 > declared) atomicOr(a.err, PVQ_ERR_STACK);
     }
 }
 
@@ -322,6 +468,17 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     size_t oSOff = carve((size_t)(S + 2) * sizeof(long long));
     size_t oErr = carve(sizeof(int));
     size_t oTemp = carve(tempBytes);
+    // VQ streams: scaled lines, workspaces and band bit buffers of one batch of channel-blocks at a time
+    // (band layouts the batched back end is not sized for stay in k_encode)
+    const bool vq = ctx->cfg.use_vq != 0 && ctx->host.longBands.nBands <= EPRE_SLOTS &&
+                    PAC_SUBFRAMES * ctx->host.shortBands.nBands <= EPRE_SLOTS && ctx->host.sbrNOmitted <= 4;
+    const long long batchCb = vq ? std::min<long long>(nCh, ENC_BATCH_CB) : 0, batchGroups = (batchCb + 31) / 32;
+    size_t oPre = carve((size_t)batchCb * sizeof(EncPre));
+    size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));
+    size_t oWs = carve((size_t)batchGroups * 32 * 2 * EPRE_WS_PER_CB * sizeof(double));
+    size_t oY = carve((size_t)batchGroups * 32 * EPRE_WS_PER_CB * sizeof(int));
+    size_t oWords = carve((size_t)batchGroups * 32 * EPRE_WORDS_PER_CB * sizeof(unsigned));
+    size_t oPerm = carve((size_t)(batchCb + 2) * sizeof(int));
     void* scr = nullptr;
     if ((rc = pac_scratch(ctx, o, &scr))) return rc;
     unsigned char* sb = (unsigned char*)scr;
@@ -337,13 +494,26 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
     size_t smem = enc_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
+    a.pre = nullptr; a.preLines = nullptr; a.perm = nullptr; a.counts = nullptr; a.cb0 = 0; a.nBatch = (int)nCh;
+    PAC_CHECK(cudaFuncSetAttribute(k_encode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaEventRecord(ctx->ev[0], st);
-    if (ctx->cfg.precision == PAC_F32) {
-        PAC_CHECK(cudaFuncSetAttribute(k_encode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_encode<float><<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
-    } else {
-        PAC_CHECK(cudaFuncSetAttribute(k_encode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_encode<double><<<(unsigned)nCh, ENC_NT, smem, st>>>(ctx->dev, a);
+    for (long long q0 = 0; q0 < nCh; q0 += vq ? batchCb : nCh) {
+        const long long nq = vq ? std::min(batchCb, nCh - q0) : nCh;
+        a.cb0 = (int)q0; a.nBatch = (int)nq;
+        if (vq) {
+            a.pre = (EncPre*)(sb + oPre); a.preLines = (double*)(sb + oLines);
+            a.perm = (int*)(sb + oPerm); a.counts = a.perm + batchCb;
+            PAC_CHECK(cudaMemsetAsync(a.counts, 0, 2 * sizeof(int), st));
+        }
+        if (ctx->cfg.precision == PAC_F32) k_encode<float><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
+        else k_encode<double><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
+        if (vq) {
+            const int nChunks = (int)((nq + PQ_NT - 1) / PQ_NT);
+            k_pvq<<<(unsigned)(nChunks * EPRE_SLOTS), PQ_NT, 0, st>>>(ctx->dev, a, nChunks, (double*)(sb + oWs), (int*)(sb + oY),
+                                                                   (unsigned*)(sb + oWords));
+            k_pack<<<(unsigned)((nq + PK_WARPS - 1) / PK_WARPS), PK_WARPS * 32, 0, st>>>(ctx->dev, a, (unsigned*)(sb + oWords));
+        }
     }
     cudaEventRecord(ctx->ev[1], st);
     ctx->evValid[0] = 1;

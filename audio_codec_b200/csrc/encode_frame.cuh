@@ -34,6 +34,27 @@ __device__ __forceinline__ double pcm_to_double(short c) {
     return c < 0 ? -v : v;
 }
 
+// Batched back end of VQ streams (encode.cu): k_encode stops after the bit allocation and leaves the
+// scaled lines and this header; k_pvq quantises one band per thread; k_pack assembles the record.
+// slot = sub-frame * nBands + band.
+#define EPRE_SLOTS 48             // 17 long bands, or 8 sub-frames x 6 short bands
+#define EPRE_WS_PER_CB 2048       // bound on the sum of the bands' power-of-two capacities (each < 2 nLines)
+#define EPRE_WORDS_PER_CB 704     // bit buffers: nLines / 2 + 3 words per band (16 bits per line at most)
+struct EncPre {
+    double env[4];                    // SBR envelope value of each omitted band (coder/codec.py:508-510)
+    unsigned short used[EPRE_SLOTS];  // bits the band emitted (k_pvq)
+    unsigned char ba[EPRE_SLOTS];     // bit allocation; k_pvq zeroes it when the band emits nothing (codec.py:352-353)
+    unsigned char scale[PAC_SUBFRAMES];
+    unsigned char flags;              // bit 2 last, 1 cur, 0 next transient
+    unsigned char zeroSub;            // a short sub-frame of this channel is all zero (coder/pacfile.py:503-506)
+    unsigned char pad[2];
+    int p;                            // position in the batch's dense order (long blocks from the front, transient from the back)
+};
+struct EncPreOut { EncPre* hdr; double* lines; int sf; };     // lines: this block's column of the interleaved line array
+__device__ __forceinline__ size_t epre_line_index(long long p, int k) {
+    return ((size_t)(p >> 5) * 1024 + (size_t)k) * 32 + (size_t)(p & 31);
+}
+
 // ---------------------------------------------------------------- per-frame encode
 struct EncSmem {
     double* xs;        // [2048] frame samples; later PVQ workspace A
@@ -117,7 +138,7 @@ __device__ __forceinline__ double block_max(double v, double* red, int tid) {
 // are instruction-cache bound otherwise).  flags: 1 long frame, 2 SBR, 4 transient block,
 // 8 last-or-next-transient.  S.lines holds the scaled MDCT lines, S.smr the SMRs, S.env the SBR sums.
 static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, unsigned char* raw, EncLog lg, int flags,
-                                               int scale, int* bpos, int* err) {
+                                               int scale, int* bpos, int* err, EncPreOut po) {
     EncSmem S;
     enc_smem_carve(raw, S);
     S.logVal = lg.val; S.logW = lg.w; S.logCnt = lg.cnt; S.logCap = lg.cap;
@@ -143,6 +164,36 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
         }
         if (lane < nB) S.capOff[lane] = ci - c;
         if (lane == nB - 1) S.capOff[nB] = ci;
+    }
+    if (po.hdr) {
+        // batched path: warp 0 allocates bits while the other warps move the scaled lines out
+        __syncthreads();
+        if (warp != 0) {
+            for (int i = tid - 32; i < H; i += ENC_NT - 32)
+                po.lines[(size_t)(po.sf * PAC_HALF_SHORT + i) * 32] = S.lines[i];
+        } else {
+            int nfb = H;
+            if (!sbr) {
+                if (cur) nfb = (int)(1.45 * H);
+                if (lastOrNext) nfb = (int)(0.85 * nfb);
+            }
+            double budget = dev->targetBitsPerSample * (double)nfb;
+            budget -= (double)dev->nScaleBits;
+            budget -= (double)(dev->nMantSizeBits * nB);
+            warp_bit_alloc(budget, dev->maxMantBits, nB, S.nlEff, S.smr, S.tmp, S.ba);
+            __syncwarp();
+            if (lane < nB) {
+                po.hdr->ba[po.sf * nB + lane] = (unsigned char)S.ba[lane];
+                if (sbr && bands.omitted[lane]) {
+                    int k = 0;
+                    for (int q = 0; q < lane; ++q) k += bands.omitted[q] ? 1 : 0;
+                    if (k < 4) po.hdr->env[k] = (S.env[lane] * up) / (double)bands.nLines[lane];
+                }
+            }
+            if (lane == 0) po.hdr->scale[po.sf] = (unsigned char)scale;
+        }
+        __syncthreads();
+        return 0;
     }
     // PVQ ping-pong workspaces: a long frame reuses its dead sample / FFT buffers; a short
     // sub-frame must leave xs intact for its siblings and uses the tail of lines[]
@@ -351,7 +402,7 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
 // path); bit allocation and quantisation are always fp64 + integer.
 template <int N, typename T>
 __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const T* fx, int shape, bool cur,
-                            bool lastOrNext, bool sbr, int* bpos, int* err) {
+                            bool lastOrNext, bool sbr, int* bpos, int* err, EncPreOut po = {nullptr, nullptr, 0}) {
     constexpr int H = N / 2, Q = N / 4;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
@@ -414,5 +465,5 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     PHASE(2);
     const int flags = (N == PAC_NLONG ? 1 : 0) | (sbr ? 2 : 0) | (cur ? 4 : 0) | (lastOrNext ? 8 : 0);
     const EncLog lg = {S.logVal, S.logW, S.logCnt, S.logCap};
-    return encode_back(dev, S.raw, lg, flags, scale, bpos, err);
+    return encode_back(dev, S.raw, lg, flags, scale, bpos, err, po);
 }

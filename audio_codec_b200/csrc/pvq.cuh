@@ -304,26 +304,28 @@ struct BandEnc {
 
 // np.add.reduce of |a[i]| in NumPy's pairwise order (loops_utils.h.src pairwise_sum): blocks of at
 // most 128 elements are summed with 8 accumulators, larger arrays are halved recursively.
+template <int XS = 1>   // XS: element stride (the batched quantiser interleaves 32 lanes)
 static __device__ __noinline__ double np_abs_sum_block(const double* a, int n) {
     if (n < 8) {
         double r = 0.0;
-        for (int i = 0; i < n; ++i) r += fabs(a[i]);
+        for (int i = 0; i < n; ++i) r += fabs(a[i * XS]);
         return r;
     }
     double r[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) r[j] = fabs(a[j]);
+    for (int j = 0; j < 8; ++j) r[j] = fabs(a[j * XS]);
     int i;
     for (i = 8; i < n - (n % 8); i += 8) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] += fabs(a[i + j]);
+        for (int j = 0; j < 8; ++j) r[j] += fabs(a[(i + j) * XS]);
     }
     double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
-    for (; i < n; ++i) res += fabs(a[i]);
+    for (; i < n; ++i) res += fabs(a[i * XS]);
     return res;
 }
+template <int XS = 1>
 __device__ __forceinline__ double np_abs_sum(const double* a, int n) {
-    if (n <= 128) return np_abs_sum_block(a, n);
+    if (n <= 128) return np_abs_sum_block<XS>(a, n);
     // explicit post-order walk of the halving tree (depth <= 4 for n <= 1024)
     struct Fr { const double* p; int n; int state; double left; };
     Fr st[8];
@@ -332,11 +334,11 @@ __device__ __forceinline__ double np_abs_sum(const double* a, int n) {
     double ret = 0.0;
     while (sp > 0) {
         Fr& f = st[sp - 1];
-        if (f.n <= 128) { ret = np_abs_sum_block(f.p, f.n); --sp; continue; }
+        if (f.n <= 128) { ret = np_abs_sum_block<XS>(f.p, f.n); --sp; continue; }
         int n2 = f.n / 2;
         n2 -= n2 % 8;
         if (f.state == 0) { f.state = 1; st[sp++] = {f.p, n2, 0, 0.0}; continue; }
-        if (f.state == 1) { f.left = ret; f.state = 2; st[sp++] = {f.p + n2, f.n - n2, 0, 0.0}; continue; }
+        if (f.state == 1) { f.left = ret; f.state = 2; st[sp++] = {f.p + n2 * XS, f.n - n2, 0, 0.0}; continue; }
         ret = f.left + ret;
         --sp;
     }
@@ -344,38 +346,39 @@ __device__ __forceinline__ double np_abs_sum(const double* a, int n) {
 }
 
 // quantize_pvq for one leaf on ONE thread (coder/gain_shape_quantize.py:41-54, :105-124).
+template <int XS = 1>
 __device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& t, const double* vec, double* res, int* y,
                                                                   int n, long long K, int* err) {
     if (K == 0) return 0ull;
-    const double l1 = np_abs_sum(vec, n);
+    const double l1 = np_abs_sum<XS>(vec, n);
     if (l1 == 0.0) { *err |= PVQ_ERR_DEGENERATE; return 0ull; }
     long long ps = 0;
     for (int i = 0; i < n; ++i) {
-        double xh = fabs(((double)K * vec[i]) / l1);
+        double xh = fabs(((double)K * vec[i * XS]) / l1);
         double p = floor(xh);
-        res[i] = xh - p;
-        y[i] = (int)p;
+        res[i * XS] = xh - p;
+        y[i * XS] = (int)p;
         ps += (long long)p;
     }
     for (long long rem = K - ps; rem > 0; --rem) {        // np.argmax: first maximum
         double bv = res[0];
         int bi = 0;
         for (int i = 1; i < n; ++i) {
-            double r = res[i];
+            double r = res[i * XS];
             if (r > bv) { bv = r; bi = i; }
         }
-        res[bi] -= 1.0;
-        y[bi] += 1;
+        res[bi * XS] -= 1.0;
+        y[bi * XS] += 1;
     }
     unsigned long long acc = 0ull;
     long long k = K;
     for (int i = 0; i < n && k > 0; ++i) {
-        const int a = y[i];
+        const int a = y[i * XS];
         if (a > 0) {
             const int l = n - i;
             const unsigned long long below = pvq_N(t, l - 1, k - a);
             unsigned long long c = pvq_N(t, l, k) - pvq_N(t, l, k - a) - below;
-            if (vec[i] < 0.0) c += below;
+            if (vec[i * XS] < 0.0) c += below;
             acc += c;
             k -= a;
         }
@@ -516,4 +519,114 @@ __device__ __forceinline__ void cta_quantize_leaves(const PvqTab& t, const TNode
         if (logVal && nd.logSlot >= 0 && nd.logSlot < logCap) logVal[(size_t)nd.band * logCap + nd.logSlot] = idx;
         if (werr) atomicOr(err, werr);
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// quantize_gain_shape for one band in ONE THREAD (k_pvq, encode.cu): the 32 lanes of a warp hold the
+// same band of 32 different channel-blocks.  The tree is walked depth first, so the fields come out
+// in stream order and go through a register bit accumulator into the band's private word buffer
+// (written once per word, no read-modify-write).  Same arithmetic as warp_quantize_gain_shape with
+// the level-synchronous encoder's table lookups (theta_terms / ms_alloc_l2t); sums run in index order.
+// x, wsA, wsB, yws, words: per-lane arrays with element stride XS (lane-interleaved global memory).
+struct TBitW { unsigned* w; unsigned long long acc; int n, widx, cap; };
+template <int XS>
+__device__ __forceinline__ void tbw_put32(TBitW& b, unsigned v, int w) {       // w in 1..32
+    b.acc = (b.acc << w) | (unsigned long long)(w == 32 ? v : (v & ((1u << w) - 1u)));
+    b.n += w;
+    if (b.n >= 32) {
+        if (b.widx < b.cap) b.w[b.widx * XS] = (unsigned)(b.acc >> (b.n - 32));
+        ++b.widx;
+        b.n -= 32;
+    }
+}
+template <int XS>
+__device__ __forceinline__ void tbw_put(TBitW& b, unsigned long long v, int w) {   // w in 0..64
+    if (w > 32) { tbw_put32<XS>(b, (unsigned)(v >> 32), w - 32); w = 32; }
+    if (w > 0) tbw_put32<XS>(b, (unsigned)v, w);
+}
+template <int XS>
+__device__ __forceinline__ int tbw_flush(TBitW& b) {
+    const int total = b.widx * 32 + b.n;
+    if (b.n > 0 && b.widx < b.cap) b.w[b.widx * XS] = (unsigned)(b.acc << (32 - b.n));
+    return total;
+}
+
+// Returns the number of bits written (0: all-zero band, caller zeroes bitAlloc).  env: the band is
+// ONE value, envVal (SBR envelope, coder/codec.py:508-510), instead of x[0..L).
+template <int XS>
+__device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const double* __restrict__ x, bool env,
+                                                          double envVal, int L, int R, double* wsA, double* wsB, int* yws,
+                                                          int cap, unsigned* words, int capWords, int* err) {
+    int bg, bs;
+    gs_alloc(t, R, L, &bg, &bs);
+    double ss = 0.0;
+    if (env) ss = envVal * envVal;
+    else for (int i = 0; i < L; ++i) { const double v = x[i * XS]; ss += v * v; }
+    const double gain = sqrt(ss);
+    if (gain == 0.0) return 0;
+    TBitW out = {words, 0ull, 0, 0, capWords};
+    if (bs != 0) {
+        if (env) wsA[0] = envVal / gain;
+        else {
+#pragma unroll 4
+            for (int i = 0; i < L; ++i) wsA[i * XS] = x[i * XS] / gain;
+        }
+        PvqNode st[24];
+        int sp = 0, used = 0;
+        st[sp++] = {0, (short)cap, (short)L, 0, bs};
+        while (sp > 0) {
+            const PvqNode nd = st[--sp];
+            double* __restrict__ cur = (nd.buf ? wsB : wsA) + nd.off * XS;
+            double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+            if (nd.bits <= PVQ_SPLIT_BITS) {
+                long long K;
+                int w;
+                pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
+                const unsigned long long idx = thread_quantize_pvq<XS>(t, cur, oth, yws + nd.off * XS, nd.n, K, err);
+                tbw_put<XS>(out, idx, w);
+                used += w;
+                continue;
+            }
+            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+            double sm = 0.0, sd = 0.0;
+#pragma unroll 4
+            for (int i = 0; i < half; ++i) {
+                const double l = i < mid ? cur[i * XS] : 0.0;     // odd n: the LEFT half is zero padded at its end
+                const double r = cur[(mid + i) * XS];
+                const double M = (l + r) / 2.0, S = (l - r) / 2.0;
+                oth[i * XS] = M;
+                oth[(hc + i) * XS] = S;
+                sm += M * M;
+                sd += S * S;
+            }
+            const double nm = sqrt(sm), ns = sqrt(sd);
+#pragma unroll 4
+            for (int i = 0; i < half; ++i) {
+                if (nm != 0.0) oth[i * XS] = oth[i * XS] / nm;
+                if (ns != 0.0) oth[(hc + i) * XS] = oth[(hc + i) * XS] / ns;
+            }
+            const double theta = nm == 0.0 ? 0.0 : pm_atan(ns / nm);
+            int aT, aMs, aMid, aSide, entry;
+            gs_alloc(t, nd.bits, half, &aT, &aMs);
+            const double hp = 1.5707963267948966;        // np.pi / 2
+            if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+            const unsigned long long ti = quantize_uniform(theta / hp, aT);
+            double tq, l2t;
+            theta_terms(t, ti, aT, &tq, &l2t, &entry);
+            ms_alloc_l2t(aMs, tq, l2t, half, &aMid, &aSide);
+            tbw_put<XS>(out, ti, aT);
+            used += aT;
+            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
+            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide};
+            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid};
+        }
+        bg += bs - used;
+    }
+    const double g = pm_log(1.0 + 255.0 * (gain / (double)L)) / log(256.0);      // mu_law_fn
+    if (bg < 0) bg = 0;
+    if (bg > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; bg = 64; }
+    tbw_put<XS>(out, quantize_uniform(g, bg), bg);
+    const int total = tbw_flush<XS>(out);
+    if (out.widx >= capWords && total > capWords * 32) *err |= PVQ_ERR_STACK;
+    return total;
 }
