@@ -163,7 +163,10 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
 // block is band nB-1-q; of a transient block, sub-frame q / 6, band 5 - q % 6.  Lines go to
 // lines[pre_line_index(cb, k)]; the workspaces are lane-interleaved the same way.
 #define DQ_NT 128
-__global__ void __launch_bounds__(DQ_NT)
+#ifndef DQ_MINB
+#define DQ_MINB 1
+#endif
+__global__ void __launch_bounds__(DQ_NT, DQ_MINB)
 k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, int nChunks, CbHdr* __restrict__ hdrs,
           double* __restrict__ lines, double* __restrict__ ws, const int* __restrict__ perm,
           const int* __restrict__ counts) {

@@ -216,7 +216,10 @@ __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, i
     *cap = c0;
     *wbase = wb + f * wall;
 }
-__global__ void __launch_bounds__(PQ_NT)
+#ifndef PQ_MINB
+#define PQ_MINB 1
+#endif
+__global__ void __launch_bounds__(PQ_NT, PQ_MINB)
 k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict__ ws, int* __restrict__ yws,
       unsigned* __restrict__ words) {
     const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;

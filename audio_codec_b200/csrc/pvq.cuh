@@ -566,33 +566,56 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
     if (gain == 0.0) return 0;
     TBitW out = {words, 0ull, 0, 0, capWords};
     if (bs != 0) {
-        if (env) wsA[0] = envVal / gain;
-        else {
-#pragma unroll 4
-            for (int i = 0; i < L; ++i) wsA[i * XS] = x[i * XS] / gain;
-        }
-        PvqNode st[24];
+        // A node's vector stays UN-normalised in the workspace; its norm travels with the node and the
+        // reader divides (the same operations on the same values as normalise-then-read, without the
+        // extra load + store pass per level).  The root reads the lines themselves, norm = gain.
+        struct TEncNode { short off, cap, n, buf; int bits; double nr; };
+        TEncNode st[24];
         int sp = 0, used = 0;
-        st[sp++] = {0, (short)cap, (short)L, 0, bs};
+        if (env) wsA[0] = envVal / gain;
+        st[sp++] = {0, (short)cap, (short)L, 0, bs, env ? 0.0 : gain};
+        bool root = true;
         while (sp > 0) {
-            const PvqNode nd = st[--sp];
-            double* __restrict__ cur = (nd.buf ? wsB : wsA) + nd.off * XS;
+            const TEncNode nd = st[--sp];
+            const double* cur = (root && !env) ? x : ((nd.buf ? wsB : wsA) + nd.off * XS);
             double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+            const double nr = nd.nr;
             if (nd.bits <= PVQ_SPLIT_BITS) {
                 long long K;
                 int w;
                 pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
-                const unsigned long long idx = thread_quantize_pvq<XS>(t, cur, oth, yws + nd.off * XS, nd.n, K, err);
+                // the leaf search reads its vector three times: normalise it once, in place (a root leaf: into wsA)
+                double* vec = (nd.buf ? wsB : wsA) + nd.off * XS;
+                if (nr != 0.0 && K != 0) {
+                    int i = 0;
+                    for (; i + 4 <= nd.n; i += 4) {
+                        const double v0 = cur[i * XS], v1 = cur[(i + 1) * XS], v2 = cur[(i + 2) * XS], v3 = cur[(i + 3) * XS];
+                        vec[i * XS] = v0 / nr; vec[(i + 1) * XS] = v1 / nr; vec[(i + 2) * XS] = v2 / nr; vec[(i + 3) * XS] = v3 / nr;
+                    }
+                    for (; i < nd.n; ++i) vec[i * XS] = cur[i * XS] / nr;
+                }
+                const unsigned long long idx = thread_quantize_pvq<XS>(t, vec, oth, yws + nd.off * XS, nd.n, K, err);
                 tbw_put<XS>(out, idx, w);
                 used += w;
+                root = false;
                 continue;
             }
             const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
             double sm = 0.0, sd = 0.0;
-#pragma unroll 4
-            for (int i = 0; i < half; ++i) {
-                const double l = i < mid ? cur[i * XS] : 0.0;     // odd n: the LEFT half is zero padded at its end
-                const double r = cur[(mid + i) * XS];
+            const bool dv = nr != 0.0;
+            int i = 0;
+            for (; i + 2 <= mid; i += 2) {                 // two elements per trip: four loads in flight
+                double l0 = cur[i * XS], l1 = cur[(i + 1) * XS], r0 = cur[(mid + i) * XS], r1 = cur[(mid + i + 1) * XS];
+                if (dv) { l0 = l0 / nr; l1 = l1 / nr; r0 = r0 / nr; r1 = r1 / nr; }
+                const double M0 = (l0 + r0) / 2.0, S0 = (l0 - r0) / 2.0, M1 = (l1 + r1) / 2.0, S1 = (l1 - r1) / 2.0;
+                oth[i * XS] = M0; oth[(hc + i) * XS] = S0; oth[(i + 1) * XS] = M1; oth[(hc + i + 1) * XS] = S1;
+                sm += M0 * M0; sd += S0 * S0;
+                sm += M1 * M1; sd += S1 * S1;
+            }
+            for (; i < half; ++i) {
+                double l = i < mid ? cur[i * XS] : 0.0;           // odd n: the LEFT half is zero padded at its end
+                double r = cur[(mid + i) * XS];
+                if (dv) { l = l / nr; r = r / nr; }
                 const double M = (l + r) / 2.0, S = (l - r) / 2.0;
                 oth[i * XS] = M;
                 oth[(hc + i) * XS] = S;
@@ -600,11 +623,6 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
                 sd += S * S;
             }
             const double nm = sqrt(sm), ns = sqrt(sd);
-#pragma unroll 4
-            for (int i = 0; i < half; ++i) {
-                if (nm != 0.0) oth[i * XS] = oth[i * XS] / nm;
-                if (ns != 0.0) oth[(hc + i) * XS] = oth[(hc + i) * XS] / ns;
-            }
             const double theta = nm == 0.0 ? 0.0 : pm_atan(ns / nm);
             int aT, aMs, aMid, aSide, entry;
             gs_alloc(t, nd.bits, half, &aT, &aMs);
@@ -616,9 +634,10 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
             ms_alloc_l2t(aMs, tq, l2t, half, &aMid, &aSide);
             tbw_put<XS>(out, ti, aT);
             used += aT;
+            root = false;
             if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
-            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide};
-            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid};
+            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, ns};
+            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid, nm};
         }
         bg += bs - used;
     }
