@@ -16,7 +16,7 @@
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include "encode_frame.cuh"
-#define ENC_BATCH_CB 32768       // channel-blocks per k_encode / k_pvq / k_pack round (bounds the scratch: ~52 KB each)
+#define ENC_BATCH_CB 32768       // channel-blocks per k_encode / k_bitalloc / k_pvq / k_pack round (bounds the scratch: ~52 KB each)
 #include "pac_api.h"
 
 // ---------------------------------------------------------------- transient detector
@@ -198,6 +198,41 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
 }
 
 // ---------------------------------------------------------------- batched VQ back end
+// k_bitalloc: one warp per channel-block runs the water-filling allocation of its frames
+// (coder/codec.py:288-299, :446-453; coder/bitalloc.py:62-145) from the SMRs k_encode left.  Serial in
+// the passes, so it runs here at full occupancy instead of on one warp of a waiting 8-warp CTA.
+#define BA_WARPS 8
+__global__ void __launch_bounds__(BA_WARPS * 32)
+k_bitalloc(const PacDev* __restrict__ dev, EncArgs a) {
+    __shared__ double s_smr[BA_WARPS][32], s_tmp[BA_WARPS][32];
+    __shared__ int s_nl[BA_WARPS][32], s_ba[BA_WARPS][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int local = blockIdx.x * BA_WARPS + warp;
+    if (local >= a.nBatch) return;
+    EncPre* h = a.pre + local;
+    const bool last = (h->flags >> 2) & 1, cur = (h->flags >> 1) & 1, nxt = h->flags & 1;
+    const PacBands& bands = cur ? dev->shortBands : dev->longBands;
+    const int nB = bands.nBands, nF = cur ? PAC_SUBFRAMES : 1, H = cur ? PAC_HALF_SHORT : PAC_HALF_LONG;
+    const bool sbr = !cur && dev->useSBR;
+    int nfb = H;
+    if (!sbr) {
+        if (cur) nfb = (int)(1.45 * H);
+        if (last || nxt) nfb = (int)(0.85 * nfb);
+    }
+    double budget = dev->targetBitsPerSample * (double)nfb;
+    budget -= (double)dev->nScaleBits;
+    budget -= (double)(dev->nMantSizeBits * nB);
+    if (lane < nB) s_nl[warp][lane] = (sbr && bands.omitted[lane]) ? 1 : bands.nLines[lane];
+    for (int f = 0; f < nF; ++f) {
+        if (lane < nB) s_smr[warp][lane] = h->smr[f * nB + lane];
+        __syncwarp();
+        warp_bit_alloc(budget, dev->maxMantBits, nB, s_nl[warp], s_smr[warp], s_tmp[warp], s_ba[warp]);
+        __syncwarp();
+        if (lane < nB) h->ba[f * nB + lane] = (unsigned char)s_ba[warp][lane];
+        __syncwarp();
+    }
+}
+
 // k_pvq: one thread per (channel-block, band).  A CTA holds one band slot of PQ_NT consecutive blocks
 // of the dense order; CTAs are ordered widest band first.  Slot q of a long block is band nB-1-q; of
 // a transient block, sub-frame q / 6, band 5 - q % 6.
@@ -513,6 +548,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
         else k_encode<double><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
         if (vq) {
             const int nChunks = (int)((nq + PQ_NT - 1) / PQ_NT);
+            k_bitalloc<<<(unsigned)((nq + BA_WARPS - 1) / BA_WARPS), BA_WARPS * 32, 0, st>>>(ctx->dev, a);
             k_pvq<<<(unsigned)(nChunks * EPRE_SLOTS), PQ_NT, 0, st>>>(ctx->dev, a, nChunks, (double*)(sb + oWs), (int*)(sb + oY),
                                                                    (unsigned*)(sb + oWords));
             k_pack<<<(unsigned)((nq + PK_WARPS - 1) / PK_WARPS), PK_WARPS * 32, 0, st>>>(ctx->dev, a, (unsigned*)(sb + oWords));

@@ -42,6 +42,7 @@ __device__ __forceinline__ double pcm_to_double(short c) {
 #define EPRE_WORDS_PER_CB 704     // bit buffers: nLines / 2 + 3 words per band (16 bits per line at most)
 struct EncPre {
     double env[4];                    // SBR envelope value of each omitted band (coder/codec.py:508-510)
+    double smr[EPRE_SLOTS];           // signal-to-mask ratio per band (k_encode -> k_bitalloc)
     unsigned short used[EPRE_SLOTS];  // bits the band emitted (k_pvq)
     unsigned char ba[EPRE_SLOTS];     // bit allocation; k_pvq zeroes it when the band emits nothing (codec.py:352-353)
     unsigned char scale[PAC_SUBFRAMES];
@@ -166,32 +167,18 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
         if (lane == nB - 1) S.capOff[nB] = ci;
     }
     if (po.hdr) {
-        // batched path: warp 0 allocates bits while the other warps move the scaled lines out
-        __syncthreads();
-        if (warp != 0) {
-            for (int i = tid - 32; i < H; i += ENC_NT - 32)
-                po.lines[(size_t)(po.sf * PAC_HALF_SHORT + i) * 32] = S.lines[i];
-        } else {
-            int nfb = H;
-            if (!sbr) {
-                if (cur) nfb = (int)(1.45 * H);
-                if (lastOrNext) nfb = (int)(0.85 * nfb);
+        // (no barrier needed before: S.lines / S.smr / S.env were completed behind barriers of steps 1-3)
+        // batched path: the scaled lines, the SMRs and the envelope values leave for k_bitalloc / k_pvq
+        for (int i = tid; i < H; i += ENC_NT) po.lines[(size_t)(po.sf * PAC_HALF_SHORT + i) * 32] = S.lines[i];
+        if (tid < nB) {
+            po.hdr->smr[po.sf * nB + tid] = S.smr[tid];
+            if (sbr && bands.omitted[tid]) {
+                int k = 0;
+                for (int q = 0; q < tid; ++q) k += bands.omitted[q] ? 1 : 0;
+                if (k < 4) po.hdr->env[k] = (S.env[tid] * up) / (double)bands.nLines[tid];
             }
-            double budget = dev->targetBitsPerSample * (double)nfb;
-            budget -= (double)dev->nScaleBits;
-            budget -= (double)(dev->nMantSizeBits * nB);
-            warp_bit_alloc(budget, dev->maxMantBits, nB, S.nlEff, S.smr, S.tmp, S.ba);
-            __syncwarp();
-            if (lane < nB) {
-                po.hdr->ba[po.sf * nB + lane] = (unsigned char)S.ba[lane];
-                if (sbr && bands.omitted[lane]) {
-                    int k = 0;
-                    for (int q = 0; q < lane; ++q) k += bands.omitted[q] ? 1 : 0;
-                    if (k < 4) po.hdr->env[k] = (S.env[lane] * up) / (double)bands.nLines[lane];
-                }
-            }
-            if (lane == 0) po.hdr->scale[po.sf] = (unsigned char)scale;
         }
+        if (tid == 0) po.hdr->scale[po.sf] = (unsigned char)scale;
         __syncthreads();
         return 0;
     }
