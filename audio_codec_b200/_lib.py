@@ -48,6 +48,8 @@ def _load():
         "pac_encode_host": (i, [vp, vp, C.POINTER(i), C.POINTER(i), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
         "pac_decode_host": (i, [vp, vp, C.POINTER(ll), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
         "pac_last_kernel_ms": (i, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+        "pac_kernel_stats": (i, [vp, i, C.POINTER(C.c_float), C.POINTER(i)]),
+        "pac_kernel_launches": (ll, [vp]),
         "pac_decode_plan": (i, [vp, vp, C.POINTER(ll), i, C.POINTER(ll), vp]),
         "pac_decode_streams": (i, [vp, vp, C.POINTER(ll), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
         # per-function ops
@@ -81,6 +83,7 @@ def _load():
 lib = _load()
 EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola",
            "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams", "pac_last_kernel_ms",
+           "pac_kernel_stats", "pac_kernel_launches",
            "pac_encode_host", "pac_decode_host",
            "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_bit_alloc", "pac_quantize_uniform",
            "pac_dequantize_uniform", "pac_scale_factor", "pac_mantissa", "pac_dequantize", "pac_gain_shape_quantize",
@@ -135,6 +138,15 @@ class Context:
         e, d = C.c_float(), C.c_float()
         check(lib.pac_last_kernel_ms(self.h, C.byref(e), C.byref(d)))
         return e.value, d.value
+
+    def kernel_stats(self, kind):
+        """(device ms, launches) of kernel `kind` (0 k_encode, 1 k_pvq, 2 k_dequant, 3 k_decode) in the last call."""
+        ms, n = C.c_float(), C.c_int()
+        check(lib.pac_kernel_stats(self.h, kind, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def kernel_launches(self):
+        return int(lib.pac_kernel_launches(self.h))
 
     def close(self):
         if getattr(self, "h", None):

@@ -385,6 +385,8 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     // a trailing partial block (fewer than C channel-blocks) lands in the C spare slots and is ignored
     k_walk<<<(S + WALK_WARPS - 1) / WALK_WARPS, WALK_WARPS * 32, 0, st>>>(d_pac, (long long*)(sb + oSOff), S, pac_header_bytes(ctx), nullptr,
                                             (long long*)(sb + oCbOff), (long long*)(sb + oPay), (int*)(sb + oPayB));
+    ctx->kevN[2] = ctx->kevN[3] = 0;
+    ctx->launches += 2;       // k_walk, twice (count, then offsets)
     const int oneChunk[2] = {0, S};
     if (!chunks) { chunks = oneChunk; n_chunks = 1; }
     for (int c = 0; c < n_chunks; ++c) {
@@ -410,16 +412,22 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
                 int* dCounts = dPerm + batchCb;
                 PAC_CHECK(cudaMemsetAsync(dCounts, 0, 2 * sizeof(int), st));
                 k_hdr<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre, dPerm, dCounts);
+                pac_kev_begin(ctx, 2, st);
                 k_dequant<<<(unsigned)(nChunks * PRE_SLOTS), DQ_NT, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, nChunks, dPre, dLines,
                                                                           (double*)(sb + oWs), dPerm, dCounts);
+                pac_kev_end(ctx, 2, st);
+                ++ctx->launches;      // k_hdr
             }
+            pac_kev_begin(ctx, 3, st);
             if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
             else k_decode<double><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
+            pac_kev_end(ctx, 3, st);
         }
         if (c == 0) { cudaEventRecord(ctx->ev[3], st); ctx->evValid[1] = 1; }
         PAC_CHECK(cudaGetLastError());
     }
     const long long g0 = pcmOff[s0] / 1024, nOut = pcmOff[s1] / 1024 - g0;
+    if (nOut > 0) ++ctx->launches;
     if (nOut > 0)
         k_ola<<<(unsigned)nOut, 256, 0, st>>>((const double*)(sb + oFrames), (long long*)(sb + oCbOff),
                                               (long long*)(sb + oPcmOff), S, C, d_pcm, g0);

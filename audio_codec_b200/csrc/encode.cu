@@ -527,6 +527,8 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     unsigned char* dTmpl = (unsigned char*)(dHdr + (S + 1));
     PAC_CHECK(cudaMemcpyAsync(dBlkOff, hBlkOff, hostInts * sizeof(int) + 128, cudaMemcpyHostToDevice, st));
     PAC_CHECK(cudaMemsetAsync(sb + oErr, 0, sizeof(int), st));
+    ctx->kevN[0] = ctx->kevN[1] = 0;
+    ctx->launches += 6;       // k_transient, k_sizes, the two kernels of the cub scan, k_gather, k_headers (per batch below: k_encode, k_bitalloc, k_pvq, k_pack)
     k_transient<<<(unsigned)totBlk, 128, 0, st>>>(d_pcm, dBlkOff, dNb, S, C, sb + oDet);
     EncArgs a;
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
@@ -544,13 +546,18 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
             a.perm = (int*)(sb + oPerm); a.counts = a.perm + batchCb;
             PAC_CHECK(cudaMemsetAsync(a.counts, 0, 2 * sizeof(int), st));
         }
+        pac_kev_begin(ctx, 0, st);
         if (ctx->cfg.precision == PAC_F32) k_encode<float><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
         else k_encode<double><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
+        pac_kev_end(ctx, 0, st);
         if (vq) {
             const int nChunks = (int)((nq + PQ_NT - 1) / PQ_NT);
             k_bitalloc<<<(unsigned)((nq + BA_WARPS - 1) / BA_WARPS), BA_WARPS * 32, 0, st>>>(ctx->dev, a);
+            pac_kev_begin(ctx, 1, st);
             k_pvq<<<(unsigned)(nChunks * EPRE_SLOTS), PQ_NT, 0, st>>>(ctx->dev, a, nChunks, (double*)(sb + oWs), (int*)(sb + oY),
                                                                    (unsigned*)(sb + oWords));
+            pac_kev_end(ctx, 1, st);
+            ctx->launches += 2;
             k_pack<<<(unsigned)((nq + PK_WARPS - 1) / PK_WARPS), PK_WARPS * 32, 0, st>>>(ctx->dev, a, (unsigned*)(sb + oWords));
         }
     }

@@ -372,6 +372,11 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     c->pinned = nullptr;
     c->pinnedBytes = 0;
     for (int i = 0; i < 4; ++i) cudaEventCreate(&c->ev[i]);
+    for (int k = 0; k < 4; ++k) {
+        c->kevN[k] = 0;
+        for (int j = 0; j < PAC_KEV_MAX; ++j) { cudaEventCreate(&c->kev[k][j][0]); cudaEventCreate(&c->kev[k][j][1]); }
+    }
+    c->launches = 0;
     c->evValid[0] = c->evValid[1] = 0;
     c->io[0] = c->io[1] = nullptr;
     c->ioBytes[0] = c->ioBytes[1] = 0;
@@ -421,6 +426,8 @@ extern "C" void pac_destroy(pac_ctx* c) {
     if (c->pinned) cudaFreeHost(c->pinned);
     for (int i = 0; i < 2; ++i) if (c->io[i]) cudaFree(c->io[i]);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(c->ev[i]);
+    for (int k = 0; k < 4; ++k)
+        for (int j = 0; j < PAC_KEV_MAX; ++j) { cudaEventDestroy(c->kev[k][j][0]); cudaEventDestroy(c->kev[k][j][1]); }
     if (c->cpReady)
     {
         for (int i = 0; i < 2; ++i) { cudaStreamDestroy(c->cp[i]); cudaEventDestroy(c->cpEv[i]); }
@@ -496,3 +503,22 @@ extern "C" int pac_last_kernel_ms(pac_ctx* c, float* enc_ms, float* dec_ms) {
     if (dec_ms) { *dec_ms = -1.f; if (c->evValid[1]) cudaEventElapsedTime(dec_ms, c->ev[2], c->ev[3]); }
     return 0;
 }
+
+// Device time and launch count of one kernel over the last pac_encode_streams / pac_decode_streams call
+// (kind: 0 k_encode, 1 k_pvq, 2 k_dequant, 3 k_decode); the call must have completed.
+extern "C" int pac_kernel_stats(pac_ctx* c, int kind, float* ms, int* launches) {
+    if (!c || kind < 0 || kind > 3) return PAC_ERR_ARG;
+    float tot = 0.f;
+    const int n = c->kevN[kind] < PAC_KEV_MAX ? c->kevN[kind] : PAC_KEV_MAX;
+    for (int j = 0; j < n; ++j) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, c->kev[kind][j][0], c->kev[kind][j][1]) != cudaSuccess) return PAC_ERR_ARG;
+        tot += t;
+    }
+    if (ms) *ms = tot;
+    if (launches) *launches = c->kevN[kind];
+    return 0;
+}
+
+// Kernels launched by the library on this context since pac_create.
+extern "C" long long pac_kernel_launches(pac_ctx* c) { return c ? c->launches : PAC_ERR_ARG; }

@@ -4,6 +4,7 @@
 #include "../../include/pac_b200.h"
 #include "pac_common.cuh"
 
+#define PAC_KEV_MAX 64
 struct pac_ctx {
     int device;
     pac_config cfg;
@@ -23,11 +24,25 @@ struct pac_ctx {
     int cpReady;
     cudaEvent_t ev[4];   // around k_encode and k_decode, for pac_last_kernel_ms
     int evValid[2];
+    // per-kernel device time of the last encode / decode call: events around every launch of
+    // 0 k_encode, 1 k_pvq, 2 k_dequant, 3 k_decode (one launch per batch of channel-blocks)
+    cudaEvent_t kev[4][PAC_KEV_MAX][2];
+    int kevN[4];
+    long long launches;  // kernels launched by the library on this context
     // windows of arbitrary length for pac_window, built on demand
     struct WinEntry { int kind, N, Ns; double alpha; const double* d; const float* f; };
     std::vector<WinEntry> winCache;
 };
 
+// events around one kernel launch (kind as in kev); launches beyond PAC_KEV_MAX per call go untimed
+static inline void pac_kev_begin(pac_ctx* c, int kind, cudaStream_t st) {
+    if (c->kevN[kind] < PAC_KEV_MAX) cudaEventRecord(c->kev[kind][c->kevN[kind]][0], st);
+}
+static inline void pac_kev_end(pac_ctx* c, int kind, cudaStream_t st) {
+    if (c->kevN[kind] < PAC_KEV_MAX) cudaEventRecord(c->kev[kind][c->kevN[kind]][1], st);
+    ++c->kevN[kind];
+    ++c->launches;
+}
 int pac_scratch(pac_ctx* ctx, size_t bytes, void** out);
 int pac_pinned(pac_ctx* ctx, size_t bytes, void** out);
 int pac_io(pac_ctx* ctx, int which, size_t bytes, void** out);

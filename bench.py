@@ -327,6 +327,9 @@ def main():
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     enc_ms, dec_ms = [], []
+    kern = {k: [] for k in ("k_encode", "k_pvq", "k_dequant", "k_decode")}
+    kern_n = {}
+    launches0 = ctx.kernel_launches()
     torch.cuda.synchronize()
     e0.record()
     for _ in range(args.steps):
@@ -334,7 +337,12 @@ def main():
         a, b = ctx.last_kernel_ms()
         enc_ms.append(a)
         dec_ms.append(b)
+        for kind, name in enumerate(kern):          # events around every launch of the four main kernels
+            ms, nl = ctx.kernel_stats(kind)
+            kern[name].append(ms)
+            kern_n[name] = nl
     e1.record()
+    launches = ctx.kernel_launches() - launches0
     torch.cuda.synchronize()
     dev_ms = e0.elapsed_time(e1)
     sampler.stop.set()
@@ -373,7 +381,10 @@ def main():
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        ke_ms = float(np.mean(enc_ms))
+        # dominant kernel: k_encode (window + MDCT, Hann FFT, psychoacoustic model), one launch per batch of
+        # channel-blocks; its launches of a step together process every channel-block once
+        ke_ms = float(np.mean(kern["k_encode"]))
+        ke_n = max(1, kern_n["k_encode"])
         algo = n_chblocks * ALGO_BYTES_PER_CHBLOCK_IN + pac_bytes
         ach = algo / (ke_ms * 1e-3) / 1e9
         line = {"metric": "encoded audio-sec/sec (enc+dec, 128 kb/s)", "value": world * audio_s * args.steps / (dev_ms * 1e-3),
@@ -385,19 +396,25 @@ def main():
                            "parallelism": f"streams sharded over {world} GPU(s), no collective on the data path"},
                 "e2e": {"value": world * audio_s * args.steps / (host_ms_scaled * 1e-3), "unit": "audio-s/s",
                         "h2d_bytes_per_step": d_pcm.numel() * 2 + pac_bytes, "d2h_bytes_per_step": pac_bytes + int(po[-1]) * 2},
-                # per step: k_transient, k_encode, k_sizes, 2 x cub scan, k_gather, k_headers; 2 x k_walk, k_decode, k_ola
-                "gpu_launches": 11 * args.steps,
+                # counted by the library (pac_kernel_launches): per step k_transient, per batch k_encode / k_bitalloc /
+                # k_pvq / k_pack, k_sizes, scan, k_gather, k_headers; 2 x k_walk, per batch k_hdr / k_dequant / k_decode, k_ola
+                "gpu_launches": int(launches),
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "kernel": "k_encode", "achieved": ach, "peak": peak, "unit": "GB/s",
                              "frac": ach / peak, "traffic": None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                             "k_encode_ms": ke_ms, "k_decode_ms": float(np.mean(dec_ms)),
-                             "note": "encode is compute/latency bound (fp64 psychoacoustics + PVQ), see DESIGN.md"}}
+                             "launches_per_step": ke_n, "avg_launch_ms": ke_ms / ke_n,
+                             "algorithmic_bytes_per_launch": algo / ke_n,
+                             "kernels_ms_per_step": {k: float(np.mean(v)) for k, v in kern.items()},
+                             "kernel_launches_per_step": dict(kern_n),
+                             "k_encode_ms": float(np.mean(enc_ms)), "k_decode_ms": float(np.mean(dec_ms)),
+                             "stage_note": "k_encode_ms / k_decode_ms are the whole encode / decode stages (events around all their kernels)",
+                             "note": "k_encode is compute bound (fp64 psychoacoustic model: ~3 transcendentals per line), see DESIGN.md"}}
         try:        # dram bytes per k_encode launch from the committed ncu capture of this same configuration
             tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
             if tr.get("streams") == S and tr.get("seconds") == SECONDS:
                 line["roofline"]["traffic"] = tr["k_encode_dram_bytes"]
-                line["roofline"]["traffic_k_decode"] = tr.get("k_decode_dram_bytes")
+                line["roofline"]["traffic_other_kernels"] = {k: v for k, v in tr.items() if k.endswith("_dram_bytes") and k != "k_encode_dram_bytes"}
         except Exception:
             pass
         if not args.no_mdct:

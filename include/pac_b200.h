@@ -120,9 +120,15 @@ int pac_decode_host(pac_ctx* ctx, const unsigned char* h_pac, const long long* h
                     short* h_pcm, long long pcm_capacity, long long* h_pcm_off, int* h_err, void* stream);
 
 /* Measurement aid (no reference counterpart): device milliseconds of the dominant
- * kernel (k_encode / k_decode) of the last encode / decode call on this context,
+ * stage (k_encode .. k_pack / k_hdr .. k_decode) of the last encode / decode call on this context,
  * from CUDA events recorded on the caller's stream; -1 if none yet. */
 int pac_last_kernel_ms(pac_ctx* ctx, float* enc_ms, float* dec_ms);
+/* The same per kernel: device milliseconds summed over the launches (one per batch of channel-blocks)
+ * of kind 0 k_encode, 1 k_pvq, 2 k_dequant, 3 k_decode in the last completed encode / decode call,
+ * and how many launches that was. */
+int pac_kernel_stats(pac_ctx* ctx, int kind, float* ms, int* launches);
+/* Kernels launched by the library on this context since pac_create. */
+long long pac_kernel_launches(pac_ctx* ctx);
 
 
 /* ======================================================================================
