@@ -106,8 +106,10 @@ struct EncArgs {
     int cb0, nBatch;
 };
 
-template <typename T>
-__global__ void __launch_bounds__(ENC_NT, 3)
+// FRONT: the batched path (a.pre set): stops after the psychoacoustic model, needs enc_front_smem_bytes()
+// only and runs four CTAs per SM.
+template <typename T, bool FRONT>
+__global__ void __launch_bounds__(ENC_NT, FRONT ? 4 : 3)
 k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EncSmem S;
@@ -139,18 +141,18 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
         int blk = i < 1024 ? priorBlk : dataBlk;
         xs[i] = blk < 0 ? (T)0 : (T)pcm_to_double(base[(long long)blk * 1024 + (i & 1023)]);
     }
-    for (int i = tid; i < REC_WORDS; i += ENC_NT) S.blockbuf[i] = 0u;
+    if (!FRONT) for (int i = tid; i < REC_WORDS; i += ENC_NT) S.blockbuf[i] = 0u;
     if (tid == 0) {
         S.misc[3] = 0;
         S.misc[4] = 0;
     }
     __syncthreads();
-    if (tid == 0 && a.pre) {                  // dense order for k_pvq: its warps hold blocks of one kind
+    if (tid == 0 && FRONT) {                  // dense order for k_pvq: its warps hold blocks of one kind
         const int p = cur ? a.nBatch - 1 - atomicAdd(&a.counts[1], 1) : atomicAdd(&a.counts[0], 1);
         a.perm[p] = blockIdx.x;
         S.misc[8] = p;
     }
-    if (tid == 0) {                           // 3 flag bits (coder/pacfile.py:575-577)
+    if (tid == 0 && !FRONT) {                 // 3 flag bits (coder/pacfile.py:575-577)
         BitW bw = {S.blockbuf, 0};
         bw_put(bw, last, 1);
         bw_put(bw, cur, 1);
@@ -160,7 +162,7 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     __syncthreads();
     int declared = 4;                         // "+4 for block switching" (pacfile.py:560)
     EncPreOut po = {nullptr, nullptr, 0};
-    if (a.pre) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); }
+    if (FRONT) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); }
     if (!cur) {
         int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
         declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err, po);
@@ -178,7 +180,7 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
         }
     }
     __syncthreads();
-    if (a.pre) {                              // the record is assembled by k_pack
+    if (FRONT) {                              // the record is assembled by k_pack
         if (tid == 0) {
             po.hdr->flags = (unsigned char)((last ? 4 : 0) | (cur ? 2 : 0) | (nxt ? 1 : 0));
             po.hdr->zeroSub = (unsigned char)S.misc[4];
@@ -535,8 +537,11 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
     size_t smem = enc_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
     a.pre = nullptr; a.preLines = nullptr; a.perm = nullptr; a.counts = nullptr; a.cb0 = 0; a.nBatch = (int)nCh;
-    PAC_CHECK(cudaFuncSetAttribute(k_encode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    PAC_CHECK(cudaFuncSetAttribute(k_encode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smemF = enc_front_smem_bytes();
+    PAC_CHECK(cudaFuncSetAttribute(k_encode<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
     cudaEventRecord(ctx->ev[0], st);
     for (long long q0 = 0; q0 < nCh; q0 += vq ? batchCb : nCh) {
         const long long nq = vq ? std::min(batchCb, nCh - q0) : nCh;
@@ -547,8 +552,13 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
             PAC_CHECK(cudaMemsetAsync(a.counts, 0, 2 * sizeof(int), st));
         }
         pac_kev_begin(ctx, 0, st);
-        if (ctx->cfg.precision == PAC_F32) k_encode<float><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
-        else k_encode<double><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
+        if (vq) {
+            if (ctx->cfg.precision == PAC_F32) k_encode<float, true><<<(unsigned)nq, ENC_NT, smemF, st>>>(ctx->dev, a);
+            else k_encode<double, true><<<(unsigned)nq, ENC_NT, smemF, st>>>(ctx->dev, a);
+        } else {
+            if (ctx->cfg.precision == PAC_F32) k_encode<float, false><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
+            else k_encode<double, false><<<(unsigned)nq, ENC_NT, smem, st>>>(ctx->dev, a);
+        }
         pac_kev_end(ctx, 0, st);
         if (vq) {
             const int nChunks = (int)((nq + PQ_NT - 1) / PQ_NT);

@@ -92,6 +92,11 @@ __host__ __device__ constexpr size_t enc_smem_bytes() {
            ENC_MAX_NODES * sizeof(TNode) + 32 * sizeof(BandEnc);
 }
 
+// The arrays only the in-CTA quantiser and packer use come last: the batched front end (k_encode with
+// EncArgs::pre) runs with enc_front_smem_bytes() and one more CTA per SM.
+__host__ __device__ constexpr size_t enc_front_smem_bytes() {
+    return (2048 + 2048 + 1024 + 1040 + 32 + 32 + 16 + 32) * sizeof(double) + (32 * 4 + 34 * 2 + 16) * sizeof(int);
+}
 __device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
     double* dp = reinterpret_cast<double*>(raw);
     S.raw = raw;
@@ -103,10 +108,7 @@ __device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
     S.tmp = dp; dp += 32;
     S.red = dp; dp += 16;
     S.env = dp; dp += 32;
-    unsigned* up = reinterpret_cast<unsigned*>(dp);
-    S.blockbuf = up; up += REC_WORDS;
-    S.bandbits = up; up += BAND_WORDS;
-    int* ip = reinterpret_cast<int*>(up);
+    int* ip = reinterpret_cast<int*>(dp);
     S.ba = ip; ip += 32;
     S.nlEff = ip; ip += 32;
     S.used = ip; ip += 32;
@@ -114,7 +116,10 @@ __device__ __forceinline__ void enc_smem_carve(unsigned char* raw, EncSmem& S) {
     S.capOff = ip; ip += 34;
     S.sfb = ip; ip += 32;
     S.misc = ip; ip += 16;
-    S.nodes = reinterpret_cast<TNode*>(ip);
+    unsigned* up = reinterpret_cast<unsigned*>(ip);
+    S.blockbuf = up; up += REC_WORDS;
+    S.bandbits = up; up += BAND_WORDS;
+    S.nodes = reinterpret_cast<TNode*>(up);
     S.bandEnc = reinterpret_cast<BandEnc*>(S.nodes + ENC_MAX_NODES);
     S.logVal = nullptr; S.logW = nullptr; S.logCnt = nullptr; S.logCap = 0;
 }
