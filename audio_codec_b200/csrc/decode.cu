@@ -221,12 +221,13 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
     if (werr) atomicOr(a.err, werr);
 }
 
-template <typename T>
-__global__ void __launch_bounds__(DEC_NT, 3)
+// PRE: behind k_dequant (preAll set): SBR + IMDCT only, dec_lean_smem_bytes(), four CTAs per SM.
+template <typename T, bool PRE>
+__global__ void __launch_bounds__(DEC_NT, PRE ? 4 : 3)
 k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DecSmem S;
-    dec_smem_carve(smem_raw, S);
+    dec_smem_carve(smem_raw, S, PRE);
     const int tid = threadIdx.x;
     const long long cb = (long long)blockIdx.x + a.cb0;
     int nBytes = a.payBytes[cb];
@@ -234,7 +235,7 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ pr
         if (tid == 0) atomicOr(a.err, PVQ_ERR_STACK);
         nBytes = DEC_REC_MAX;
     }
-    const CbHdr* pre = preAll ? preAll + blockIdx.x : nullptr;
+    const CbHdr* pre = PRE ? preAll + blockIdx.x : nullptr;
     const unsigned char* src = a.buf + a.payOff[cb];
     if (!pre) for (int i = tid; i < nBytes; i += DEC_NT) S.rec[i] = src[i];
     for (int i = tid; i < 2048; i += DEC_NT) S.y[i] = 0.0;
@@ -398,8 +399,11 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
         a.bufBytes = h_stream_off[S];
         size_t smem = dec_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
-        PAC_CHECK(cudaFuncSetAttribute(k_decode<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        PAC_CHECK(cudaFuncSetAttribute(k_decode<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const size_t smemL = dec_lean_smem_bytes();
+        PAC_CHECK(cudaFuncSetAttribute(k_decode<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemL));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemL));
         if (c == 0) cudaEventRecord(ctx->ev[2], st);      // pac_last_kernel_ms: the first chunk (the only one unless chunked)
         for (long long q0 = 0; q0 < nCbC; q0 += vq ? batchCb : nCbC) {
             const long long nq = vq ? std::min(batchCb, nCbC - q0) : nCbC;
@@ -419,8 +423,13 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
                 ++ctx->launches;      // k_hdr
             }
             pac_kev_begin(ctx, 3, st);
-            if (ctx->cfg.precision == PAC_F32) k_decode<float><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
-            else k_decode<double><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
+            if (vq) {
+                if (ctx->cfg.precision == PAC_F32) k_decode<float, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines);
+                else k_decode<double, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines);
+            } else {
+                if (ctx->cfg.precision == PAC_F32) k_decode<float, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
+                else k_decode<double, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
+            }
             pac_kev_end(ctx, 3, st);
         }
         if (c == 0) { cudaEventRecord(ctx->ev[3], st); ctx->evValid[1] = 1; }
