@@ -574,13 +574,59 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
         int sp = 0, used = 0;
         if (env) wsA[0] = envVal / gain;
         st[sp++] = {0, (short)cap, (short)L, 0, bs, env ? 0.0 : gain};
-        bool root = true;
-        while (sp > 0) {
-            const TEncNode nd = st[--sp];
-            const double* cur = (root && !env) ? x : ((nd.buf ? wsB : wsA) + nd.off * XS);
-            double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
-            const double nr = nd.nr;
-            if (nd.bits <= PVQ_SPLIT_BITS) {
+        bool root = true, fail = false;
+        // Each round: (1) split nodes until a leaf is on top of the stack, (2) quantise that leaf.  The lanes
+        // of a warp (same band, 32 blocks) so meet at the pulse search, the long step.
+        while (sp > 0 && !fail) {
+            while (sp > 0 && st[sp - 1].bits > PVQ_SPLIT_BITS) {
+                const TEncNode nd = st[--sp];
+                const double* cur = (root && !env) ? x : ((nd.buf ? wsB : wsA) + nd.off * XS);
+                double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+                const double nr = nd.nr;
+                const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
+                double sm = 0.0, sd = 0.0;
+                const bool dv = nr != 0.0;
+                int i = 0;
+                for (; i + 2 <= mid; i += 2) {                 // two elements per trip: four loads in flight
+                    double l0 = cur[i * XS], l1 = cur[(i + 1) * XS], r0 = cur[(mid + i) * XS], r1 = cur[(mid + i + 1) * XS];
+                    if (dv) { l0 = l0 / nr; l1 = l1 / nr; r0 = r0 / nr; r1 = r1 / nr; }
+                    const double M0 = (l0 + r0) / 2.0, S0 = (l0 - r0) / 2.0, M1 = (l1 + r1) / 2.0, S1 = (l1 - r1) / 2.0;
+                    oth[i * XS] = M0; oth[(hc + i) * XS] = S0; oth[(i + 1) * XS] = M1; oth[(hc + i + 1) * XS] = S1;
+                    sm += M0 * M0; sd += S0 * S0;
+                    sm += M1 * M1; sd += S1 * S1;
+                }
+                for (; i < half; ++i) {
+                    double l = i < mid ? cur[i * XS] : 0.0;           // odd n: the LEFT half is zero padded at its end
+                    double r = cur[(mid + i) * XS];
+                    if (dv) { l = l / nr; r = r / nr; }
+                    const double M = (l + r) / 2.0, S = (l - r) / 2.0;
+                    oth[i * XS] = M;
+                    oth[(hc + i) * XS] = S;
+                    sm += M * M;
+                    sd += S * S;
+                }
+                const double nm = sqrt(sm), ns = sqrt(sd);
+                const double theta = nm == 0.0 ? 0.0 : pm_atan(ns / nm);
+                int aT, aMs, aMid, aSide, entry;
+                gs_alloc(t, nd.bits, half, &aT, &aMs);
+                const double hp = 1.5707963267948966;        // np.pi / 2
+                if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+                const unsigned long long ti = quantize_uniform(theta / hp, aT);
+                double tq, l2t;
+                theta_terms(t, ti, aT, &tq, &l2t, &entry);
+                ms_alloc_l2t(aMs, tq, l2t, half, &aMid, &aSide);
+                tbw_put<XS>(out, ti, aT);
+                used += aT;
+                root = false;
+                if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; fail = true; break; }
+                if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, ns};
+                if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid, nm};
+            }
+            if (sp > 0 && !fail) {
+                const TEncNode nd = st[--sp];
+                const double* cur = (root && !env) ? x : ((nd.buf ? wsB : wsA) + nd.off * XS);
+                double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+                const double nr = nd.nr;
                 long long K;
                 int w;
                 pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
@@ -598,46 +644,7 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
                 tbw_put<XS>(out, idx, w);
                 used += w;
                 root = false;
-                continue;
             }
-            const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
-            double sm = 0.0, sd = 0.0;
-            const bool dv = nr != 0.0;
-            int i = 0;
-            for (; i + 2 <= mid; i += 2) {                 // two elements per trip: four loads in flight
-                double l0 = cur[i * XS], l1 = cur[(i + 1) * XS], r0 = cur[(mid + i) * XS], r1 = cur[(mid + i + 1) * XS];
-                if (dv) { l0 = l0 / nr; l1 = l1 / nr; r0 = r0 / nr; r1 = r1 / nr; }
-                const double M0 = (l0 + r0) / 2.0, S0 = (l0 - r0) / 2.0, M1 = (l1 + r1) / 2.0, S1 = (l1 - r1) / 2.0;
-                oth[i * XS] = M0; oth[(hc + i) * XS] = S0; oth[(i + 1) * XS] = M1; oth[(hc + i + 1) * XS] = S1;
-                sm += M0 * M0; sd += S0 * S0;
-                sm += M1 * M1; sd += S1 * S1;
-            }
-            for (; i < half; ++i) {
-                double l = i < mid ? cur[i * XS] : 0.0;           // odd n: the LEFT half is zero padded at its end
-                double r = cur[(mid + i) * XS];
-                if (dv) { l = l / nr; r = r / nr; }
-                const double M = (l + r) / 2.0, S = (l - r) / 2.0;
-                oth[i * XS] = M;
-                oth[(hc + i) * XS] = S;
-                sm += M * M;
-                sd += S * S;
-            }
-            const double nm = sqrt(sm), ns = sqrt(sd);
-            const double theta = nm == 0.0 ? 0.0 : pm_atan(ns / nm);
-            int aT, aMs, aMid, aSide, entry;
-            gs_alloc(t, nd.bits, half, &aT, &aMs);
-            const double hp = 1.5707963267948966;        // np.pi / 2
-            if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
-            const unsigned long long ti = quantize_uniform(theta / hp, aT);
-            double tq, l2t;
-            theta_terms(t, ti, aT, &tq, &l2t, &entry);
-            ms_alloc_l2t(aMs, tq, l2t, half, &aMid, &aSide);
-            tbw_put<XS>(out, ti, aT);
-            used += aT;
-            root = false;
-            if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; break; }
-            if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, (short)(1 - nd.buf), aSide, ns};
-            if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, (short)(1 - nd.buf), aMid, nm};
         }
         bg += bs - used;
     }
