@@ -369,7 +369,9 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     // (band layouts the batched front end is not sized for fall back to the in-CTA parse of decode_front)
     const bool vq = ctx->cfg.use_vq != 0 && ctx->host.longBands.nBands <= PRE_SLOTS &&
                     PAC_SUBFRAMES * ctx->host.shortBands.nBands <= PRE_SLOTS && ctx->host.sbrNOmitted <= 4;
-    const long long batchCb = vq ? std::min<long long>(nCb, DEC_BATCH_CB) : 0;
+    const char* envB = getenv("PAC_BATCH_CB");                 // test hook: small batches exercise the batch loop
+    const long long maxB = envB && atoll(envB) > 0 ? atoll(envB) : DEC_BATCH_CB;
+    const long long batchCb = vq ? std::min<long long>(nCb, maxB) : 0;
     const long long batchGroups = (batchCb + 31) / 32;
     size_t oPre = carve((size_t)batchCb * sizeof(CbHdr));
     size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));

@@ -512,7 +512,9 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     // (band layouts the batched back end is not sized for stay in k_encode)
     const bool vq = ctx->cfg.use_vq != 0 && ctx->host.longBands.nBands <= EPRE_SLOTS &&
                     PAC_SUBFRAMES * ctx->host.shortBands.nBands <= EPRE_SLOTS && ctx->host.sbrNOmitted <= 4;
-    const long long batchCb = vq ? std::min<long long>(nCh, ENC_BATCH_CB) : 0, batchGroups = (batchCb + 31) / 32;
+    const char* envB = getenv("PAC_BATCH_CB");                 // test hook: small batches exercise the batch loop
+    const long long maxB = envB && atoll(envB) > 0 ? atoll(envB) : ENC_BATCH_CB;
+    const long long batchCb = vq ? std::min<long long>(nCh, maxB) : 0, batchGroups = (batchCb + 31) / 32;
     size_t oPre = carve((size_t)batchCb * sizeof(EncPre));
     size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));
     size_t oWs = carve((size_t)batchGroups * 32 * 2 * EPRE_WS_PER_CB * sizeof(double));
