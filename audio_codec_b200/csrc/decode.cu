@@ -170,6 +170,9 @@ __global__ void __launch_bounds__(DQ_NT, DQ_MINB)
 k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, int nChunks, CbHdr* __restrict__ hdrs,
           double* __restrict__ lines, double* __restrict__ ws, const int* __restrict__ perm,
           const int* __restrict__ counts) {
+    __shared__ int s_off[PAC_PVQ_LMAX + 2];                  // row offsets of the N(L,K) table: read by every pvq_N call
+    for (int i = threadIdx.x; i < PAC_PVQ_LMAX + 2; i += DQ_NT) s_off[i] = dev->pvqRowOff[i];
+    __syncthreads();
     const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
     const int pos = chunk * DQ_NT + threadIdx.x;
     const int nLong = counts[0], nShort = counts[1];
@@ -209,7 +212,7 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
     long long bit0;
     BitR br = rec_reader(a, cbBase + local, &nBytes, &bit0);
     br.pos = bit0 + h->pos[slot];
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
+    PvqTab pt = {dev->pvqN, s_off, dev->log2tab, dev->pvqKW, dev->thetaTab};
     int werr = 0;
     if (env) {                                                 // one envelope value (coder/codec.py:111-132)
         double v;

@@ -259,6 +259,9 @@ __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, i
 __global__ void __launch_bounds__(PQ_NT, PQ_MINB)
 k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict__ ws, int* __restrict__ yws,
       unsigned* __restrict__ words) {
+    __shared__ int s_off[PAC_PVQ_LMAX + 2];                  // row offsets of the N(L,K) table: read by every pvq_N call
+    for (int i = threadIdx.x; i < PAC_PVQ_LMAX + 2; i += PQ_NT) s_off[i] = dev->pvqRowOff[i];
+    __syncthreads();
     const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
     const int pos = chunk * PQ_NT + threadIdx.x;
     const int nLong = a.counts[0], nShort = a.counts[1];
@@ -284,7 +287,7 @@ k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict
     double* wsB = wsA + (size_t)EPRE_WS_PER_CB * 32;
     int* y = yws + (grp * EPRE_WS_PER_CB + (size_t)base) * 32 + ln;
     unsigned* w = words + (grp * EPRE_WORDS_PER_CB + (size_t)wbase) * 32 + ln;
-    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, dev->thetaTab};
+    PvqTab pt = {dev->pvqN, s_off, dev->log2tab, dev->pvqKW, dev->thetaTab};
     int werr = 0;
     const int used = thread_quantize_gain_shape<32>(pt, x, env, (env && k < 4) ? h->env[k] : 0.0, L, R, wsA, wsB, y, cap, w,
                                                     nl / 2 + 3, &werr);
