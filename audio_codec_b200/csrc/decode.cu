@@ -14,7 +14,7 @@
 #include "pac_api.h"
 
 extern "C" int pac_header_bytes(const pac_ctx* ctx);
-#define DEC_BATCH_CB 65536       // channel-blocks per k_hdr / k_dequant / k_decode round (bounds the scratch: 32 KB each)
+#define DEC_BATCH_CB 131072      // channel-blocks per k_hdr / k_dequant / k_decode round (bounds the scratch: 40 KB each)
 
 // pass 0: count channel-blocks; pass 1: record payload offsets (absolute, past the prefix).
 // The prefix chain is serial, but its cost is the memory latency per hop: one WARP per stream

@@ -16,7 +16,7 @@
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include "encode_frame.cuh"
-#define ENC_BATCH_CB 32768       // channel-blocks per k_encode / k_bitalloc / k_pvq / k_pack round (bounds the scratch: ~52 KB each)
+#define ENC_BATCH_CB 131072      // channel-blocks per k_encode / k_bitalloc / k_pvq / k_pack round (bounds the scratch: ~52 KB each; larger batches amortise the long band-16 chains)
 #include "pac_api.h"
 
 // ---------------------------------------------------------------- transient detector
