@@ -164,7 +164,7 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
 // lines[pre_line_index(cb, k)]; the workspaces are lane-interleaved the same way.
 #define DQ_NT 128
 #ifndef DQ_MINB
-#define DQ_MINB 1
+#define DQ_MINB 6          // 80 registers (96 when free): six CTAs per SM
 #endif
 __global__ void __launch_bounds__(DQ_NT, DQ_MINB)
 k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, int nChunks, CbHdr* __restrict__ hdrs,
