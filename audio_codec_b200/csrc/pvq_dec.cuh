@@ -299,18 +299,41 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
         TDecNode st[24];
         int sp = 0, used = 0;
         st[sp++] = {0, (short)cap, (short)L, -1, 0, 0, 1, 0, bs, -1, 0.0, 0.0, 0.0};
-        while (sp > 0) {
-            const TDecNode nd = st[sp - 1];
-            double* __restrict__ cur = (nd.buf ? wsB : wsA) + nd.off * XS;
-            const double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
-            double nrOut;
-            if (nd.bits <= PVQ_SPLIT_BITS) {              // leaf
+        // Each round: (1) descend - read angles and push children until a leaf is on top, (2) decode that leaf,
+        // (3) recombine every node whose children are now complete.  The lanes of a warp (same band, 32
+        // blocks) so meet at the leaf decode, the long step, instead of each being at a different kind of node.
+        bool fail = false;
+        while (sp > 0 && !fail) {
+            while (st[sp - 1].bits > PVQ_SPLIT_BITS && st[sp - 1].state == 0) {      // (1)
+                const TDecNode nd = st[sp - 1];
+                const int half = (nd.n + 1) / 2, hc = nd.cap / 2;
+                int aT, aMs, aMid, aSide, entry;
+                gs_alloc(t, nd.bits, half, &aT, &aMs);
+                if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
+                const unsigned long long ti = br_get(br, aT);
+                used += aT;
+                double theta, l2t;
+                theta_terms(t, ti, aT, &theta, &l2t, &entry);
+                ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
+                st[sp - 1].theta = theta;
+                st[sp - 1].entry = entry;
+                st[sp - 1].state = 1;
+                st[sp - 1].z = (unsigned char)((aMid <= 0 ? 1 : 0) | (aSide <= 0 ? 2 : 0));   // children without bits read as zeros
+                if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; ones = true; fail = true; break; }
+                const short par = (short)(sp - 1);
+                if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, par, (unsigned char)(1 - nd.buf), 0, 0, 0, aSide, -1, 0.0, 0.0, 0.0};
+                if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, par, (unsigned char)(1 - nd.buf), 0, 0, 0, aMid, -1, 0.0, 0.0, 0.0};
+            }
+            if (fail) break;
+            if (st[sp - 1].bits <= PVQ_SPLIT_BITS) {                                  // (2)
+                const TDecNode nd = st[sp - 1];
+                double* cur = (nd.buf ? wsB : wsA) + nd.off * XS;
                 long long K;
                 int w;
                 pvq_k_for_bits(t, nd.n, nd.bits, &K, &w, err);
                 const unsigned long long idx = br_get(br, w);
                 used += w;
-                nrOut = sqrt(pvq_vector<XS>(t, idx, nd.n, K, cur, err));
+                double nrOut = sqrt(pvq_vector<XS>(t, idx, nd.n, K, cur, err));
                 if (nd.root) {                            // a root leaf is normalised twice (:214-218)
                     double ss = 0.0;
                     for (int i = 0; i < nd.n; ++i) {
@@ -320,28 +343,18 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
                     }
                     nrOut = sqrt(ss);
                 }
-            } else {
-                const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
-                if (nd.state == 0) {                      // first visit: theta, then children
-                    int aT, aMs, aMid, aSide, entry;
-                    gs_alloc(t, nd.bits, half, &aT, &aMs);
-                    if (aT > 64) { *err |= PVQ_ERR_FIELD_TOO_WIDE; aT = 64; }
-                    const unsigned long long ti = br_get(br, aT);
-                    used += aT;
-                    double theta, l2t;
-                    theta_terms(t, ti, aT, &theta, &l2t, &entry);
-                    ms_alloc_l2t(aMs, theta, l2t, half, &aMid, &aSide);
-                    st[sp - 1].theta = theta;
-                    st[sp - 1].entry = entry;
-                    st[sp - 1].state = 1;
-                    st[sp - 1].z = (unsigned char)((aMid <= 0 ? 1 : 0) | (aSide <= 0 ? 2 : 0));   // children without bits read as zeros
-                    if (sp + 2 > 24) { *err |= PVQ_ERR_STACK; ones = true; break; }
-                    const short par = (short)(sp - 1);
-                    if (aSide > 0) st[sp++] = {(short)(nd.off + hc), (short)hc, (short)half, par, (unsigned char)(1 - nd.buf), 0, 0, 0, aSide, -1, 0.0, 0.0, 0.0};
-                    if (aMid > 0) st[sp++] = {nd.off, (short)hc, (short)half, par, (unsigned char)(1 - nd.buf), 0, 0, 0, aMid, -1, 0.0, 0.0, 0.0};
-                    continue;
+                --sp;                                      // hand the norm to the parent (mid child: same offset)
+                if (nd.par >= 0) {
+                    if (nd.off == st[nd.par].off) st[nd.par].nrMid = nrOut; else st[nd.par].nrSide = nrOut;
+                } else {
+                    rootNr = nrOut;
                 }
-                // children done: recombine (coder/gain_shape_quantize.py:449-463)
+            }
+            while (sp > 0 && st[sp - 1].bits > PVQ_SPLIT_BITS && st[sp - 1].state == 1) {   // (3) coder/gain_shape_quantize.py:449-463
+                const TDecNode nd = st[sp - 1];
+                double* __restrict__ cur = (nd.buf ? wsB : wsA) + nd.off * XS;
+                const double* __restrict__ oth = (nd.buf ? wsA : wsB) + nd.off * XS;
+                const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
                 double ct, sn;
                 if (nd.entry >= 0) {
                     ct = t.theta[4 * nd.entry + 2];
@@ -363,13 +376,13 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
                     cur[(mid + i) * XS] = r;
                     ss += r * r;
                 }
-                nrOut = sqrt(ss);
-            }
-            --sp;                                          // hand the norm to the parent (mid child: same offset)
-            if (nd.par >= 0) {
-                if (nd.off == st[nd.par].off) st[nd.par].nrMid = nrOut; else st[nd.par].nrSide = nrOut;
-            } else {
-                rootNr = nrOut;
+                const double nrOut = sqrt(ss);
+                --sp;
+                if (nd.par >= 0) {
+                    if (nd.off == st[nd.par].off) st[nd.par].nrMid = nrOut; else st[nd.par].nrSide = nrOut;
+                } else {
+                    rootNr = nrOut;
+                }
             }
         }
         bg += bs - used;
