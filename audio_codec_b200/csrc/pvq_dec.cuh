@@ -365,8 +365,20 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
                 const double r2 = sqrt(2.0), nm = nd.nrMid, ns = nd.nrSide;
                 const bool zm = nd.z & 1, zs = nd.z & 2;
                 double ss = 0.0;
-#pragma unroll 4
-                for (int i = 0; i < half; ++i) {
+                int i = 0;
+                for (; i + 2 <= mid; i += 2) {                 // two elements per trip: up to four loads in flight
+                    double m0 = 0.0, m1 = 0.0, s0 = 0.0, s1 = 0.0;
+                    if (!zm) { m0 = oth[i * XS]; m1 = oth[(i + 1) * XS]; }
+                    if (!zs) { s0 = oth[(hc + i) * XS]; s1 = oth[(hc + i + 1) * XS]; }
+                    if (nm != 0.0) { m0 = m0 / nm; m1 = m1 / nm; }
+                    if (ns != 0.0) { s0 = s0 / ns; s1 = s1 / ns; }
+                    const double l0 = (m0 * ct + s0 * sn) / r2, r0 = (m0 * ct - s0 * sn) / r2;
+                    const double l1 = (m1 * ct + s1 * sn) / r2, r1 = (m1 * ct - s1 * sn) / r2;
+                    cur[i * XS] = l0; cur[(mid + i) * XS] = r0; cur[(i + 1) * XS] = l1; cur[(mid + i + 1) * XS] = r1;
+                    ss += l0 * l0; ss += r0 * r0;
+                    ss += l1 * l1; ss += r1 * r1;
+                }
+                for (; i < half; ++i) {
                     double m = zm ? 0.0 : oth[i * XS], s = zs ? 0.0 : oth[(hc + i) * XS];
                     if (nm != 0.0) m = m / nm;
                     if (ns != 0.0) s = s / ns;
