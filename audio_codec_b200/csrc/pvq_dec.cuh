@@ -406,11 +406,20 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
     const double sg = gq > 0.0 ? 1.0 : (gq < 0.0 ? -1.0 : 0.0);
     const double gain = sg / 255.0 * (pm_pow(256.0, fabs(gq)) - 1.0) * (double)L;     // inv_mu_law_fn * L
     const double* __restrict__ shape = wsA;
-#pragma unroll 4
-    for (int i = 0; i < L; ++i) {
-        double v = 1.0;
-        if (!ones) { v = shape[i * XS]; if (rootNr != 0.0) v = v / rootNr; }
-        out[i * XS] = ones ? gain : gain * v;
+    if (ones) {
+        for (int i = 0; i < L; ++i) out[i * XS] = gain;
+    } else {
+        int i = 0;
+        for (; i + 4 <= L; i += 4) {
+            double v0 = shape[i * XS], v1 = shape[(i + 1) * XS], v2 = shape[(i + 2) * XS], v3 = shape[(i + 3) * XS];
+            if (rootNr != 0.0) { v0 = v0 / rootNr; v1 = v1 / rootNr; v2 = v2 / rootNr; v3 = v3 / rootNr; }
+            out[i * XS] = gain * v0; out[(i + 1) * XS] = gain * v1; out[(i + 2) * XS] = gain * v2; out[(i + 3) * XS] = gain * v3;
+        }
+        for (; i < L; ++i) {
+            double v = shape[i * XS];
+            if (rootNr != 0.0) v = v / rootNr;
+            out[i * XS] = gain * v;
+        }
     }
 }
 
