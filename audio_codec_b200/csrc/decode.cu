@@ -164,7 +164,7 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
 // lines[pre_line_index(cb, k)]; the workspaces are lane-interleaved the same way.
 #define DQ_NT 128
 #ifndef DQ_MINB
-#define DQ_MINB 6          // 80 registers (96 when free): six CTAs per SM
+#define DQ_MINB 7          // 72 registers (96 when free): seven CTAs per SM (measured 5 / 6 / 7 / 8: 32.0 / 29.7 / 29.2 / 31.3 ms decode)
 #endif
 __global__ void __launch_bounds__(DQ_NT, DQ_MINB)
 k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, int nChunks, CbHdr* __restrict__ hdrs,

@@ -347,12 +347,14 @@ __device__ __forceinline__ double np_abs_sum(const double* a, int n) {
 
 // quantize_pvq for one leaf on ONE thread (coder/gain_shape_quantize.py:41-54, :105-124).
 template <int XS = 1>
-__device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& t, const double* vec, double* res, int* y,
+__device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& t, const double* __restrict__ vec,
+                                                                  double* __restrict__ res, int* __restrict__ y,
                                                                   int n, long long K, int* err) {
     if (K == 0) return 0ull;
     const double l1 = np_abs_sum<XS>(vec, n);
     if (l1 == 0.0) { *err |= PVQ_ERR_DEGENERATE; return 0ull; }
     long long ps = 0;
+#pragma unroll 4
     for (int i = 0; i < n; ++i) {
         double xh = fabs(((double)K * vec[i * XS]) / l1);
         double p = floor(xh);
