@@ -162,7 +162,9 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
 // channel-blocks; CTAs are ordered widest band first so the long chains start first.  Slot q of a long
 // block is band nB-1-q; of a transient block, sub-frame q / 6, band 5 - q % 6.  Lines go to
 // lines[pre_line_index(cb, k)]; the workspaces are lane-interleaved the same way.
+#ifndef DQ_NT
 #define DQ_NT 128
+#endif
 #ifndef DQ_MINB
 #define DQ_MINB 7          // 72 registers (96 when free): seven CTAs per SM (measured 5 / 6 / 7 / 8: 32.0 / 29.7 / 29.2 / 31.3 ms decode)
 #endif

@@ -241,7 +241,9 @@ k_bitalloc(const PacDev* __restrict__ dev, EncArgs a) {
 // k_pvq: one thread per (channel-block, band).  A CTA holds one band slot of PQ_NT consecutive blocks
 // of the dense order; CTAs are ordered widest band first.  Slot q of a long block is band nB-1-q; of
 // a transient block, sub-frame q / 6, band 5 - q % 6.
+#ifndef PQ_NT
 #define PQ_NT 128
+#endif
 __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, int b, int* base, int* cap, int* wbase) {
     int c0 = 1, bs = 0, all = 0, wb = 0, wall = 0;
     while (c0 < bands.nLines[b]) c0 <<= 1;
