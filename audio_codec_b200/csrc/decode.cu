@@ -18,10 +18,10 @@ extern "C" int pac_header_bytes(const pac_ctx* ctx);
 
 // pass 0: count channel-blocks; pass 1: record payload offsets (absolute, past the prefix).
 // The prefix chain is serial, but its cost is the memory latency per hop: one WARP per stream
-// fetches a 2 KB window (16-byte loads, all in flight together) into shared memory and lane 0
-// follows the chain inside it, so DRAM latency is paid once per ~6 records instead of per record.
+// fetches an 8 KB window (16-byte loads, all in flight together) into shared memory and lane 0
+// follows the chain inside it, so DRAM latency is paid once per ~23 records instead of per record.
 #define WALK_WARPS 4
-#define WALK_WIN 2048
+#define WALK_WIN 8192
 __global__ void __launch_bounds__(WALK_WARPS * 32)
 k_walk(const unsigned char* __restrict__ buf, const long long* __restrict__ streamOff, int nStreams,
        int headerBytes, int* __restrict__ counts, const long long* __restrict__ cbOff,
