@@ -227,10 +227,10 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
 }
 
 // PRE: behind k_dequant (preAll set): SBR + IMDCT only, dec_lean_smem_bytes(), four CTAs per SM.
-template <typename T, bool PRE>
 #ifndef DEC_PRE_MINB
 #define DEC_PRE_MINB 4
 #endif
+template <typename T, bool PRE>
 __global__ void __launch_bounds__(DEC_NT, PRE ? DEC_PRE_MINB : 3)
 k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines) {
     extern __shared__ __align__(16) unsigned char smem_raw[];

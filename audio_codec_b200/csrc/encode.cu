@@ -108,10 +108,10 @@ struct EncArgs {
 
 // FRONT: the batched path (a.pre set): stops after the psychoacoustic model, needs enc_front_smem_bytes()
 // only and runs four CTAs per SM.
-template <typename T, bool FRONT>
 #ifndef ENC_FRONT_MINB
 #define ENC_FRONT_MINB 4
 #endif
+template <typename T, bool FRONT>
 __global__ void __launch_bounds__(ENC_NT, FRONT ? ENC_FRONT_MINB : 3)
 k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
