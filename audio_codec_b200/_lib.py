@@ -39,9 +39,11 @@ def _load():
         "pac_create": (i, [i, C.POINTER(PacConfig), C.POINTER(vp)]),
         "pac_destroy": (None, [vp]),
         "pac_strerror": (C.c_char_p, [i]),
+        "pac_set_option": (i, [vp, i, d]),
         "pac_get_bands": (i, [vp, i, C.POINTER(i), C.POINTER(i)]),
         "pac_mdct_forward": (i, [vp, i, vp, ll, i, i, i, i, vp, vp]),
         "pac_imdct_ola": (i, [vp, i, vp, i, i, i, i, vp, ll, vp]),
+        "pac_mdct_direct": (i, [vp, i, vp, ll, i, i, i, vp, vp]),
         "pac_header_bytes": (i, [vp]),
         "pac_encode_bound": (ll, [vp, C.POINTER(i), i]),
         "pac_encode_streams": (i, [vp, vp, C.POINTER(i), C.POINTER(i), i, vp, ll, C.POINTER(ll), C.POINTER(i), vp]),
@@ -81,7 +83,7 @@ def _load():
 
 
 lib = _load()
-EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola",
+EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_set_option", "pac_get_bands", "pac_mdct_forward", "pac_imdct_ola", "pac_mdct_direct",
            "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams", "pac_last_kernel_ms",
            "pac_kernel_stats", "pac_kernel_launches",
            "pac_encode_host", "pac_decode_host",
@@ -127,6 +129,12 @@ class Context:
         h = C.c_void_p()
         check(lib.pac_create(self.device, C.byref(self.cfg), C.byref(h)))
         self.h = h
+
+    OPTIONS = {"batch_cb": 0, "smem_pad": 1, "host_chunk_mb": 2}
+
+    def set_option(self, name, value):
+        """Tuning knobs / test hooks (pac_set_option); 0 restores the default."""
+        check(lib.pac_set_option(self.h, self.OPTIONS[name], float(value)))
 
     def bands(self, short=False):
         n = (C.c_int * 32)()

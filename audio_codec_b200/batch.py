@@ -30,7 +30,8 @@ def _wav_info(path):
 def _read_wav(path):
     """Through the drop-in PCMFile reader, so the sample count follows the reference's header rule."""
     from .pacfile import _read_wav as rd
-    return rd(path)[1]
+    _, pcm, n_header = rd(path)
+    return pcm, n_header
 
 
 def _write_wav(path, fs, pcm):
@@ -77,12 +78,13 @@ def encode_rank(files, out_dir, rate, decode, rank, batch_seconds=4000.0):
             while j < len(fl) and (j == i or secs + fl[j][3] / fs <= batch_seconds):
                 secs += fl[j][3] / fs
                 j += 1
-            pcm = [_read_wav(f[0]) for f in fl[i:j]]
+            rd = [_read_wav(f[0]) for f in fl[i:j]]
+            pcm, n_hdr = [r[0] for r in rd], [r[1] for r in rd]
             buf, nbs = engine.pack_pcm(pcm, c)
             h_pcm = torch.from_numpy(buf).pin_memory()
             cap = _lib.lib.pac_encode_bound(ctx.h, (_lib.C.c_int * len(nbs))(*[int(v) for v in nbs]), len(nbs))
             h_out = torch.empty(int(cap), dtype=torch.uint8).pin_memory()
-            off, err = engine.encode_host(ctx, h_pcm, nbs, [p.shape[1] for p in pcm], h_out)
+            off, err = engine.encode_host(ctx, h_pcm, nbs, n_hdr, h_out)
             out = h_out.numpy()
             if decode:
                 po, _ = engine.decode_host(ctx, h_out, off, None)

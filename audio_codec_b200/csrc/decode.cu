@@ -46,7 +46,13 @@ k_walk(const unsigned char* __restrict__ buf, const long long* __restrict__ stre
         for (int j = 0; j < WALK_WIN / 512; ++j) {
             const long long o = w0 + (j * 32 + lane) * 16;
             uint4 v = make_uint4(0, 0, 0, 0);
-            if (o < bufEnd && o >= 0) v = __ldg(reinterpret_cast<const uint4*>(buf + o));
+            if (o >= 0 && o + 16 <= bufEnd) v = __ldg(reinterpret_cast<const uint4*>(buf + o));
+            else if (o + 16 > 0 && o < bufEnd) {           // first / last partial chunk of the buffer: byte loads, nothing outside [0, bufEnd)
+                __align__(16) unsigned char t[16];
+#pragma unroll
+                for (int b = 0; b < 16; ++b) t[b] = (o + b >= 0 && o + b < bufEnd) ? buf[o + b] : (unsigned char)0;
+                v = *reinterpret_cast<uint4*>(t);
+            }
             *reinterpret_cast<uint4*>(&win[warp][(j * 32 + lane) * 16]) = v;
         }
         __syncwarp();
@@ -377,8 +383,7 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     // (band layouts the batched front end is not sized for fall back to the in-CTA parse of decode_front)
     const bool vq = ctx->cfg.use_vq != 0 && ctx->host.longBands.nBands <= PRE_SLOTS &&
                     PAC_SUBFRAMES * ctx->host.shortBands.nBands <= PRE_SLOTS && ctx->host.sbrNOmitted <= 4;
-    const char* envB = getenv("PAC_BATCH_CB");                 // test hook: small batches exercise the batch loop
-    const long long maxB = envB && atoll(envB) > 0 ? atoll(envB) : DEC_BATCH_CB;
+    const long long maxB = ctx->optBatchCb > 0 ? ctx->optBatchCb : DEC_BATCH_CB;    // pac_set_option: small batches exercise the batch loop
     const long long batchCb = vq ? std::min<long long>(nCb, maxB) : 0;
     const long long batchGroups = (batchCb + 31) / 32;
     size_t oPre = carve((size_t)batchCb * sizeof(CbHdr));
@@ -408,7 +413,7 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
         a.buf = d_pac; a.payOff = (long long*)(sb + oPay); a.payBytes = (int*)(sb + oPayB);
         a.frames = (double*)(sb + oFrames); a.err = (int*)(sb + oErr);
         a.bufBytes = h_stream_off[S];
-        size_t smem = dec_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
+        size_t smem = dec_smem_bytes() + (size_t)ctx->optSmemPad;
         const size_t smemL = dec_lean_smem_bytes();
         PAC_CHECK(cudaFuncSetAttribute(k_decode<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PAC_CHECK(cudaFuncSetAttribute(k_decode<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

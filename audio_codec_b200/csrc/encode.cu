@@ -520,8 +520,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     // (band layouts the batched back end is not sized for stay in k_encode)
     const bool vq = ctx->cfg.use_vq != 0 && ctx->host.longBands.nBands <= EPRE_SLOTS &&
                     PAC_SUBFRAMES * ctx->host.shortBands.nBands <= EPRE_SLOTS && ctx->host.sbrNOmitted <= 4;
-    const char* envB = getenv("PAC_BATCH_CB");                 // test hook: small batches exercise the batch loop
-    const long long maxB = envB && atoll(envB) > 0 ? atoll(envB) : ENC_BATCH_CB;
+    const long long maxB = ctx->optBatchCb > 0 ? ctx->optBatchCb : ENC_BATCH_CB;    // pac_set_option: small batches exercise the batch loop
     const long long batchCb = vq ? std::min<long long>(nCh, maxB) : 0, batchGroups = (batchCb + 31) / 32;
     size_t oPre = carve((size_t)batchCb * sizeof(EncPre));
     size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));
@@ -545,7 +544,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     EncArgs a;
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
-    size_t smem = enc_smem_bytes() + (getenv("PAC_SMEM_PAD") ? atoi(getenv("PAC_SMEM_PAD")) : 0);
+    size_t smem = enc_smem_bytes() + (size_t)ctx->optSmemPad;
     a.pre = nullptr; a.preLines = nullptr; a.perm = nullptr; a.counts = nullptr; a.cb0 = 0; a.nBatch = (int)nCh;
     const size_t smemF = enc_front_smem_bytes();
     PAC_CHECK(cudaFuncSetAttribute(k_encode<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -23,11 +23,10 @@ static int copy_streams(pac_ctx* ctx) {
 }
 
 // Smallest chunk worth its per-call latency, in MB of PCM (the decoder scales it by the ~6:1
-// compression); PAC_HOST_CHUNK_MB overrides it (tests use tiny chunks).
-static long long chunk_mb() {
-    const char* e = getenv("PAC_HOST_CHUNK_MB");
-    const double v = e ? atof(e) : 24.0;
-    return (long long)((v > 0.0 ? v : 24.0) * 1048576.0);
+// compression); pac_set_option(PAC_OPT_HOST_CHUNK_MB) overrides it (tests use tiny chunks).
+static long long chunk_mb(const pac_ctx* ctx) {
+    const double v = ctx->optHostChunkMb > 0.0 ? ctx->optHostChunkMb : 24.0;
+    return (long long)(v * 1048576.0);
 }
 
 // Chunk boundaries (in streams): up to 6 chunks whose sizes ramp up and down (1 2 3 3 2 1), so the
@@ -59,7 +58,7 @@ static std::vector<int> chunk_bounds(const std::vector<long long>& weight, long 
 extern "C" int pac_encode_host(pac_ctx* ctx, const short* h_pcm, const int* h_nblocks, const int* h_hdr_samples,
                                int n_streams, unsigned char* h_out, long long out_capacity,
                                long long* h_stream_off, int* h_err, void* stream) {
-    if (!ctx || !h_nblocks || !h_stream_off) return PAC_ERR_ARG;
+    if (!ctx || !h_nblocks || !h_hdr_samples || !h_stream_off) return PAC_ERR_ARG;   // as pac_encode_streams
     if (n_streams <= 0) return 0;
     if (!h_pcm || !h_out) return PAC_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
@@ -70,7 +69,7 @@ extern "C" int pac_encode_host(pac_ctx* ctx, const short* h_pcm, const int* h_nb
     std::vector<long long> weight(n_streams);
     long long blocks = 0;
     for (int s = 0; s < n_streams; ++s) { weight[s] = h_nblocks[s]; blocks += h_nblocks[s]; }
-    const std::vector<int> cb = chunk_bounds(weight, std::max<long long>(1, chunk_mb() / (long long)perBlock));
+    const std::vector<int> cb = chunk_bounds(weight, std::max<long long>(1, chunk_mb(ctx) / (long long)perBlock));
     const int nChunks = (int)cb.size() - 1;
     long long bound = 0;                                    // per-chunk bounds laid end to end
     for (int c = 0; c < nChunks; ++c) bound += pac_encode_bound(ctx, h_nblocks + cb[c], cb[c + 1] - cb[c]);
@@ -104,7 +103,7 @@ extern "C" int pac_encode_host(pac_ctx* ctx, const short* h_pcm, const int* h_nb
         off.assign(ns + 1, 0);
         int e = 0;
         rc = pac_encode_streams(ctx, (const short*)((char*)dIn + (size_t)blk0[c] * perBlock), h_nblocks + s0,
-                                h_hdr_samples ? h_hdr_samples + s0 : nullptr, ns, (unsigned char*)dOut + outPos, cbound,
+                                h_hdr_samples + s0, ns, (unsigned char*)dOut + outPos, cbound,
                                 off.data(), &e, stream);
         if (rc != 0 && rc != PAC_ERR_SOFT) return rc;
         soft |= rc == PAC_ERR_SOFT;
@@ -147,7 +146,7 @@ extern "C" int pac_decode_host(pac_ctx* ctx, const unsigned char* h_pac, const l
     if ((rc = pac_io(ctx, 1, (size_t)totalAll * sizeof(short), &dOut))) return rc;
     std::vector<long long> weight(n_streams);
     for (int s = 0; s < n_streams; ++s) weight[s] = off[s + 1] - off[s];
-    const std::vector<int> cb = chunk_bounds(weight, std::max<long long>(1, chunk_mb() / 6));
+    const std::vector<int> cb = chunk_bounds(weight, std::max<long long>(1, chunk_mb(ctx) / 6));
     const int nChunks = (int)cb.size() - 1;
     // one walk, the kernels launched per chunk with an event after each: the copy stream takes every
     // finished chunk down while the next ones decode

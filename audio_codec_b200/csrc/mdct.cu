@@ -118,6 +118,47 @@ static int launch_inv(pac_ctx* ctx, const void* X, int nRows, int nFrames, int w
     return 0;
 }
 
+// ---------------------------------------------------------------- any size
+// Direct evaluation of the defining sums (coder/mdct.py:11-39 MDCTslow; MDCT/IMDCT :43-76 compute the
+// same values through an N-point FFT) for block sizes the N/4-FFT kernels do not cover: any a, b with
+// a + b even.  One thread per output value; the phase (2n + b + 1)(2k + 1) is reduced modulo 4N in
+// integers, so the cosine argument is exact.  O(N^2 / 2) per frame: meant for the small sizes of the
+// reference's self-tests and for odd window splits, not for the codec's 2048 / 256.
+template <typename T>
+__global__ void k_mdct_direct(const T* __restrict__ in, long long nRows, int a, int b, int inverse, T* __restrict__ out) {
+    const int N = a + b, H = N / 2;
+    const int nOut = inverse ? N : H, nIn = inverse ? H : N;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nRows * nOut) return;
+    const long long row = idx / nOut;
+    const int o = (int)(idx - row * nOut);
+    const T* x = in + row * nIn;
+    const long long per = 4LL * N;
+    double acc = 0.0;
+    for (int i = 0; i < nIn; ++i) {
+        const int n = inverse ? o : i, k = inverse ? i : o;
+        const long long ph = ((long long)(2 * n + b + 1) * (long long)(2 * k + 1)) % per;
+        acc += (double)x[i] * cospi((double)ph / (double)(2 * N));
+    }
+    out[idx] = (T)(inverse ? 2.0 * acc : (2.0 / (double)N) * acc);
+}
+
+extern "C" int pac_mdct_direct(pac_ctx* ctx, int dtype, const void* d_in, long long n_rows, int a, int b, int inverse,
+                               void* d_out, void* stream) {
+    if (!ctx || a < 0 || b < 0 || a + b < 2 || ((a + b) & 1)) return PAC_ERR_ARG;
+    if (n_rows <= 0) return 0;
+    if (!d_in || !d_out) return PAC_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    const long long tot = n_rows * (inverse ? a + b : (a + b) / 2);
+    const unsigned grid = (unsigned)((tot + 127) / 128);
+    if (dtype == PAC_F32) k_mdct_direct<float><<<grid, 128, 0, st>>>((const float*)d_in, n_rows, a, b, inverse, (float*)d_out);
+    else if (dtype == PAC_F64) k_mdct_direct<double><<<grid, 128, 0, st>>>((const double*)d_in, n_rows, a, b, inverse, (double*)d_out);
+    else return PAC_ERR_ARG;
+    PAC_CHECK(cudaGetLastError());
+    return 0;
+}
+
 static bool aligned16(const void* p) { return ((size_t)p & 15) == 0; }
 
 // run length of a warp's walk: long enough to amortise the one halo block, short enough that

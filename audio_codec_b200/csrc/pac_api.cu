@@ -361,10 +361,18 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     if (cfg->n_mdct_lines != PAC_HALF_LONG || cfg->n_channels < 1 || cfg->sample_rate < 8000) return PAC_ERR_ARG;
     if (cfg->n_scale_bits < 1 || cfg->n_scale_bits > 8 || cfg->n_mant_size_bits < 1 || cfg->n_mant_size_bits > 16)
         return PAC_ERR_ARG;
+    if (cfg->precision != PAC_F32 && cfg->precision != PAC_F64) return PAC_ERR_ARG;
+    {   // the device quantisers hold R = 2^nScaleBits - 1 + nMantBits magnitude bits in 64-bit integers
+        // (quant.cuh); the reference uses Python bigints.  Same bound as pac_scale_factor.
+        const int maxMant = (1 << cfg->n_mant_size_bits) > 16 ? 16 : (1 << cfg->n_mant_size_bits);
+        if ((1 << cfg->n_scale_bits) - 1 + (maxMant > 5 ? maxMant : 5) > 62) return PAC_ERR_UNSUPPORTED;
+    }
     if (cudaSetDevice(device) != cudaSuccess) return PAC_ERR_ARG;
     pac_ctx* c = new pac_ctx();
     c->device = device;
-    if (cfg->precision != PAC_F32 && cfg->precision != PAC_F64) return PAC_ERR_ARG;
+    c->optBatchCb = 0;
+    c->optSmemPad = 0;
+    c->optHostChunkMb = 0.0;
     c->cfg = *cfg;
     c->dev = nullptr;
     c->scratch = nullptr;
@@ -493,6 +501,18 @@ extern "C" int pac_get_bands(const pac_ctx* c, int which, int* n_lines, int* omi
         if (omitted) omitted[k] = b.omitted[k];
     }
     return b.nBands;
+}
+
+// Tuning knobs and test hooks (batch size of the thread-per-band kernels, shared-memory padding,
+// host pipeline chunk size).  None of them changes a result.
+extern "C" int pac_set_option(pac_ctx* c, int option, double value) {
+    if (!c || value < 0.0) return PAC_ERR_ARG;
+    switch (option) {
+        case PAC_OPT_BATCH_CB: c->optBatchCb = (long long)value; return 0;
+        case PAC_OPT_SMEM_PAD: c->optSmemPad = (int)value; return 0;
+        case PAC_OPT_HOST_CHUNK_MB: c->optHostChunkMb = value; return 0;
+        default: return PAC_ERR_ARG;
+    }
 }
 
 // Device time of the dominant kernel of the last pac_encode_streams / pac_decode_streams

@@ -29,6 +29,10 @@ struct pac_ctx {
     cudaEvent_t kev[4][PAC_KEV_MAX][2];
     int kevN[4];
     long long launches;  // kernels launched by the library on this context
+    // tuning knobs (pac_set_option): not part of the codec configuration, results do not depend on them
+    long long optBatchCb;    // channel-blocks per batch of the thread-per-band kernels (0: default)
+    int optSmemPad;          // extra dynamic shared memory for the frame kernels (occupancy experiments)
+    double optHostChunkMb;   // smallest chunk of the host-buffer pipeline, MB of PCM (0: default)
     // windows of arbitrary length for pac_window, built on demand
     struct WinEntry { int kind, N, Ns; double alpha; const double* d; const float* f; };
     std::vector<WinEntry> winCache;

@@ -121,10 +121,24 @@ def record_mismatch_rate(a, b):
     return (n - same) / max(n, 1)
 
 
-def decode_streams(pac_list, precision="f64"):
-    """Host convenience: list of .pac bytes (same configuration) -> list of int16 [C, n]."""
+def check_same_configuration(pac_list):
+    """One decode call shares one context: every stream's header must describe the same codec
+    configuration as the first (all fields but numSamples).  Returns the first header."""
     h = parse_header(pac_list[0])
-    ctx = context_for_header(h, precision)
+    for i, b in enumerate(pac_list[1:], 1):
+        g = parse_header(b)
+        bad = [k for k in h if k != "num_samples" and h[k] != g[k]]
+        if bad:
+            raise _lib.PacError(f"stream {i} differs from stream 0 in {', '.join(bad)}: decode streams of "
+                                "different configurations in separate calls")
+    return h
+
+
+def decode_streams(pac_list, precision="f64", ctx=None):
+    """Host convenience: list of .pac bytes (same configuration) -> list of int16 [C, n]."""
+    h = check_same_configuration(pac_list)
+    if ctx is None:
+        ctx = context_for_header(h, precision)
     off = np.concatenate([[0], np.cumsum([len(b) for b in pac_list])])
     d_pac = torch.from_numpy(np.frombuffer(b"".join(pac_list), dtype=np.uint8).copy()).cuda()
     d_pcm, po, err = decode_device(ctx, d_pac, off)

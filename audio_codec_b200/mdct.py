@@ -4,25 +4,46 @@ MDCT(data, a, b, isInverse=False) / IMDCT(data, a, b) keep the reference's
 signature and scaling (2/N on the forward, coder/mdct.py:63-69 / :56-62) but run
 the fused sm_100a kernel (N/4-point complex FFT).  Inputs may be NumPy arrays or
 CUDA tensors, with optional leading batch dimensions; float32 input selects the
-fp32 fast path, anything else the fp64 path.  Only the block sizes the codec
-uses are implemented (a == b, N in {2048, 256}); there is no CPU fallback.
+fp32 fast path, anything else the fp64 path.  The codec's block sizes (a == b,
+N in {2048, 256}) run the FFT kernels; every other split (any a, b with a + b
+even, e.g. the reference's self-test sizes N = 8 and N = 20, coder/mdct.py:86-107)
+runs a direct-sum kernel.  There is no CPU fallback.
 """
 import torch
 
 from . import _lib
 from ._util import from_device, ptr, to_device
 
-__all__ = ["MDCT", "IMDCT", "mdct_frames", "imdct_ola"]
+__all__ = ["MDCT", "IMDCT", "MDCTslow", "mdct_frames", "imdct_ola"]
 
 
 def _dt(t):
     return (_lib.F32, torch.float32) if t.dtype == torch.float32 else (_lib.F64, torch.float64)
 
 
+def MDCTslow(data, a, b, isInverse=False):
+    """coder/mdct.py:11-39: the defining sums, for any a, b with a + b even (direct-sum kernel)."""
+    N = int(a) + int(b)
+    if N < 2 or N % 2:
+        raise ValueError("MDCT needs an even block length a + b")
+    t, was_np = to_device(data)
+    code, dt = _dt(t)
+    t = t.to(dt)
+    n_in, n_out = (N // 2, N) if isInverse else (N, N // 2)
+    if t.shape[-1] != n_in:
+        raise ValueError(f"expected {n_in} values, got {t.shape[-1]}")
+    rows = t.reshape(-1, n_in).contiguous()
+    out = torch.empty((rows.shape[0], n_out), dtype=dt, device=t.device)
+    ctx = _lib.default_context()
+    _lib.check(_lib.lib.pac_mdct_direct(ctx.h, code, ptr(rows), rows.shape[0], int(a), int(b), int(bool(isInverse)),
+                                        ptr(out), _lib.stream_ptr()))
+    return from_device(out.reshape(*t.shape[:-1], n_out), was_np)
+
+
 def MDCT(data, a, b, isInverse=False):
     N = a + b
     if a != b or N not in (2048, 256):
-        raise ValueError("audio_codec_b200.mdct: only a == b with N in {2048, 256} is implemented on the GPU path")
+        return MDCTslow(data, a, b, isInverse)
     t, was_np = to_device(data)
     code, dt = _dt(t)
     t = t.to(dt)

@@ -43,6 +43,10 @@ class PACFile(AudioFile):
         p.omittedBands = omitted_bands(p.sfBands) if p.useSBR else []
         p.useVQ = bool(useVQ)
         p.overlapAndAdd = [np.zeros(nMDCTLines, dtype=np.float64) for _ in range(nCh)]
+        # the kernels use the band tables they build from (nMDCTLines, sampleRate): refuse any other layout
+        engine.context_for_header(dict(sample_rate=fs, n_channels=nCh, use_vq=p.useVQ, use_sbr=p.useSBR,
+                                       n_scale_bits=nScaleBits, n_mant_size_bits=nMantSizeBits,
+                                       n_lines=tuple(nLines), n_mdct_lines=nMDCTLines))
         return p
 
     def WriteFileHeader(self, codingParams):
@@ -143,20 +147,28 @@ class PACFile(AudioFile):
 
 # ---------------------------------------------------------------------- whole files, batched
 def _read_wav(path):
+    """WAV -> (params, int16 PCM [C, n_read], n_header) the way the reference's driver loop reads it:
+    PACFile.WriteFileHeader (coder/pacfile.py:309-315) adds one or two blocks to the SAME
+    codingParams.numSamples that bounds PCMFile.ReadDataBlock (coder/pcmfile.py:66-80), so the loop reads
+    up to 2048 samples past the data chunk - trailing RIFF chunks are coded as PCM, a short read is zero
+    padded.  n_header is the data-chunk count the .pac header is derived from."""
     f = __import__("audio_codec_b200.pcmfile", fromlist=["PCMFile"]).PCMFile(str(path))
     p = f.OpenForReading()
-    raw = f.fp.read(p.numSamples * p.nChannels * 2)
+    n = p.numSamples
+    n_read = n + 1024 + (1024 if n % 1024 == 0 else 0)
+    raw = f.fp.read(n_read * p.nChannels * 2)
     f.fp.close()
+    raw = raw + b"\0" * (-len(raw) % (2 * p.nChannels))
     pcm = np.frombuffer(raw, dtype="<i2").reshape(-1, p.nChannels).T
-    return p, np.ascontiguousarray(pcm)
+    return p, np.ascontiguousarray(pcm), n
 
 
 def encode_file(in_wav, out_pac, data_rate, use_vq=True, use_sbr=None):
     """WAV -> .pac with the configuration of the reference's driver (coder/pacfile.py:699-707):
     the whole file in one batched device pass (transient detection included)."""
-    p, pcm = _read_wav(in_wav)
+    p, pcm, n_header = _read_wav(in_wav)
     ctx = _lib.Context(sample_rate=p.sampleRate, n_channels=p.nChannels, rate_kbps=data_rate, use_vq=use_vq, use_sbr=use_sbr)
-    buf = engine.encode_streams(ctx, [pcm])[0]
+    buf = engine.encode_streams(ctx, [pcm], hdr_samples=[n_header])[0]
     with open(out_pac, "wb") as fp:
         fp.write(buf)
     return len(buf)

@@ -9,8 +9,8 @@
  * Conventions: plain pointers and sizes only; `stream` is a cudaStream_t passed
  * as void* (NULL = default stream); buffers named d_* are DEVICE pointers owned
  * by the caller, h_* are HOST pointers; every function returns 0 or a negative
- * pac_status; nothing throws.  One context per GPU; a context is immutable after
- * pac_create and calls on distinct streams/buffers are re-entrant.
+ * pac_status; nothing throws.  One context per GPU; the codec configuration of a
+ * context is immutable after pac_create.
  */
 #ifndef PAC_B200_H
 #define PAC_B200_H
@@ -50,8 +50,17 @@ typedef struct pac_config {
                                  * SMRs within 1e-5, decoded PCM within 1 LSB); quantisers stay fp64 + integer */
 } pac_config;
 
+/* pac_create returns PAC_ERR_UNSUPPORTED when 2^n_scale_bits - 1 + max mantissa bits exceeds 62 (the
+ * device quantisers keep magnitudes in 64-bit integers; the reference uses Python bigints there):
+ * n_scale_bits <= 5 with the default 16-bit mantissa cap. */
 int pac_create(int device, const pac_config* cfg, pac_ctx** out);
 void pac_destroy(pac_ctx* ctx);
+/* Tuning knobs / test hooks; no result depends on them.  BATCH_CB: channel-blocks per launch of the
+ * thread-per-band kernels (default 131072; small values exercise the batch loop).  SMEM_PAD: extra
+ * dynamic shared memory of the frame kernels (occupancy experiments).  HOST_CHUNK_MB: smallest chunk
+ * (MB of PCM) of the pac_encode_host / pac_decode_host copy pipeline (default 24). */
+enum pac_option { PAC_OPT_BATCH_CB = 0, PAC_OPT_SMEM_PAD = 1, PAC_OPT_HOST_CHUNK_MB = 2 };
+int pac_set_option(pac_ctx* ctx, int option, double value);
 const char* pac_strerror(int status);
 /* band layout as ScaleFactorBands(AssignMDCTLinesFromFreqLimits(..)) builds it
  * (coder/psychoac.py:106-160); which = 0 long, 1 short.  Returns nBands. */
@@ -68,6 +77,13 @@ int pac_mdct_forward(pac_ctx* ctx, int dtype, const void* d_x, long long row_str
  * (n_frames+1)*N/2 samples. */
 int pac_imdct_ola(pac_ctx* ctx, int dtype, const void* d_coefs, int n_rows, int n_frames, int N,
                   int window, void* d_y, long long row_stride, void* stream);
+
+/* mdct.MDCT / mdct.IMDCT / mdct.MDCTslow for ANY block split a, b with a + b even (coder/mdct.py:11-76;
+ * the reference's own self-test uses a = b = 4 and a = b = 10, :86-107).  Direct O(N^2 / 2) evaluation, one
+ * frame per row: d_in [n_rows][a+b] -> d_out [n_rows][(a+b)/2], or the reverse when inverse != 0.  The
+ * codec's sizes (a == b, N = 2048 / 256) go through pac_mdct_forward / pac_imdct_ola above. */
+int pac_mdct_direct(pac_ctx* ctx, int dtype, const void* d_in, long long n_rows, int a, int b, int inverse,
+                    void* d_out, void* stream);
 
 /* ---- whole-stream encode: replaces the "Encode" leg of pacfile.encode_decode_test
  * (coder/pacfile.py:674-756): PCMFile.ReadDataBlock's int16 -> float mapping

@@ -29,16 +29,16 @@ def _streams():
 
 @pytest.mark.parametrize("rate", [128, 96])
 @pytest.mark.parametrize("batch", [40, 97, 1024])
-def test_batch_size_invariance(rate, batch, monkeypatch):
+def test_batch_size_invariance(rate, batch):
     from audio_codec_b200 import _lib, engine
     fs, streams = _streams()
     ctx = _lib.Context(sample_rate=fs, n_channels=2, rate_kbps=rate)
-    monkeypatch.delenv("PAC_BATCH_CB", raising=False)
     ref_pac = engine.encode_streams(ctx, streams)
-    ref_pcm = engine.decode_streams(ref_pac)
-    monkeypatch.setenv("PAC_BATCH_CB", str(batch))
+    ref_pcm = engine.decode_streams(ref_pac, ctx=ctx)
+    ctx.set_option("batch_cb", batch)                       # pac_set_option(PAC_OPT_BATCH_CB)
     got_pac = engine.encode_streams(ctx, streams)
-    got_pcm = engine.decode_streams(ref_pac)
+    got_pcm = engine.decode_streams(got_pac, ctx=ctx)       # the small-batch encoding through the small-batch decoder
+    ctx.set_option("batch_cb", 0)
     for i, (a, b) in enumerate(zip(got_pac, ref_pac)):
         assert a == b, f"stream {i}: .pac differs with batches of {batch} channel-blocks"
     for i, (a, b) in enumerate(zip(got_pcm, ref_pcm)):

@@ -41,3 +41,18 @@ def test_error_strings():
     assert _lib.lib.pac_strerror(0) == b"ok"
     assert b"argument" in _lib.lib.pac_strerror(-1)
     assert _lib.lib.pac_create(0, None, None) == -1
+
+
+def test_create_refuses_configurations_the_quantisers_cannot_hold():
+    """pac_create argument checks run before any CUDA call: n_scale_bits = 6 needs 63 + 16 magnitude bits
+    (the reference uses Python bigints, coder/quantize.py:99-125; the device quantisers are 64-bit), so it is
+    refused as unsupported instead of silently coding garbage; so does a .pac header carrying it."""
+    import ctypes as C
+    from audio_codec_b200 import _lib
+    h = C.c_void_p()
+    for nS, want in ((6, -3), (8, -3), (9, -1), (0, -1)):
+        cfg = _lib.PacConfig(48000, 2, 1024, nS, 12, 0, 1, 128 / 48.0, 1)
+        assert _lib.lib.pac_create(0, C.byref(cfg), C.byref(h)) == want, nS
+    cfg = _lib.PacConfig(48000, 2, 1024, 4, 12, 0, 1, 128 / 48.0, 7)          # bad precision: refused before allocating
+    assert _lib.lib.pac_create(0, C.byref(cfg), C.byref(h)) == -1
+    assert _lib.lib.pac_set_option(None, 0, 1.0) == -1

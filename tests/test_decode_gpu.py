@@ -48,3 +48,24 @@ def test_encode_decode_roundtrip_48k_identical_to_oracle():
         _, yr = opac.decode_pac(ref)
         assert y.shape == yr.shape
         assert np.array_equal(y, yr), f"48k {rate}: max diff {np.abs(y.astype(int) - yr.astype(int)).max()}"
+
+
+def test_mixed_configurations_in_one_call_are_refused():
+    """One decode call shares one context (k_walk skips a fixed header size, the band tables are the context's):
+    streams of different sample rate / SBR flag in one call raise instead of decoding to garbage; a header whose
+    band table differs from the context's is refused too."""
+    from audio_codec_b200 import _lib, engine
+    a = open(os.path.join(GOLDEN, "castanet_128.pac"), "rb").read()
+    b = open(os.path.join(GOLDEN, "castanet_96.pac"), "rb").read()        # SBR stream
+    with pytest.raises(_lib.PacError, match="use_sbr"):
+        engine.decode_streams([a, b])
+    bad = bytearray(a)
+    bad[30] ^= 1                                                           # first band's line count
+    with pytest.raises(_lib.PacError, match="n_lines|band"):
+        engine.decode_streams([a, bytes(bad)])
+    with pytest.raises(_lib.PacError, match="band"):
+        engine.decode_streams([bytes(bad)])
+    bad = bytearray(a)
+    bad[18] = 6                                                            # nScaleBits = 6: unsupported by the device quantisers
+    with pytest.raises(_lib.PacError, match="unsupported"):
+        engine.decode_streams([bytes(bad)])

@@ -120,16 +120,16 @@ def test_batch_invariance_determinism_and_lengths():
 
 
 @pytest.mark.parametrize("pinned", [True, False])
-def test_host_buffer_api_chunked_pipeline_matches_device_path(pinned, monkeypatch):
+def test_host_buffer_api_chunked_pipeline_matches_device_path(pinned):
     """pac_encode_host / pac_decode_host (host buffers, chunked copy/compute pipeline) against the
     device-resident entry points on a ragged batch; chunk size forced small so several chunks form."""
     import torch
     from audio_codec_b200 import _lib, engine
-    monkeypatch.setenv("PAC_HOST_CHUNK_MB", "0.05")
     fs = 48000
     lens = [9000, 2500, 14000, 1024, 7000, 30000, 4097, 11000, 600]
     pcm = [_sig(n, fs, 300 + i) for i, n in enumerate(lens)]
     ctx = _lib.Context(sample_rate=fs, n_channels=2, rate_kbps=128)
+    ctx.set_option("host_chunk_mb", 0.05)                   # pac_set_option(PAC_OPT_HOST_CHUNK_MB): several chunks form
     want = engine.encode_streams(ctx, pcm)
     buf, nbs = engine.pack_pcm(pcm, 2)
     h_pcm = torch.from_numpy(buf)

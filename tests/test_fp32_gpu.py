@@ -40,7 +40,11 @@ def test_smr_fp32_within_tolerance():
     span = np.abs(k["frame_smr"]).max()
     err = np.abs(out["f32"] - k["frame_smr"]).max()
     print(f"SMR fp32: max abs err {err:.3e} dB over a {span:.1f} dB range (rel {err / span:.2e})")
-    assert err <= SMR_RTOL * span * 8, f"fp32 SMR error {err} dB"
+    os.makedirs("gpurun_out", exist_ok=True)            # kept with the run's evidence (copied to profiles/)
+    with open(os.path.join("gpurun_out", "smr_fp32_error.txt"), "w") as f:
+        f.write(f"SMR fp32 vs reference kats: max abs err {err:.3e} dB, range {span:.1f} dB, rel {err / span:.2e}, "
+                f"tolerance {SMR_RTOL:g}\n")
+    assert err <= SMR_RTOL * span, f"fp32 SMR error {err} dB exceeds {SMR_RTOL} x {span} dB"
 
 
 @pytest.mark.parametrize("tag", ["128", "96", "bfp128"])

@@ -286,26 +286,31 @@ def test_encode_decode_single_channel_matches_oracle(fs, rate, vq, sbr, short):
             assert [list(zip(i, w)) for i, w in zip(idx, wid)] == [[(int(v), int(w)) for v, w in f] for f in want["fields"]]
             if sbr:
                 assert all(p.sfBands.nLines[b] == 1 for b in p.omittedBands)
-            # decode: band payloads in a PackedBits, as PACFile.getDecodedBlock hands them over
-            tot = sum(sum(w) for w in wid)
+            # decode: band payloads in a PackedBits, as PACFile.getDecodedBlock hands them over; an SBR stream
+            # carries only the LAST field of an omitted band (coder/pacfile.py:385-393)
+            coded = [b for b in range(len(ba)) if ba[b]]
+            om = set(int(b) for b in po.omittedBands) if sbr else set()
+            sent = [list(zip(i, w))[-1:] if b in om else list(zip(i, w)) for b, i, w in zip(coded, idx, wid)]
+            tot = sum(n for f in sent for _, n in f)
             pb = PackedBits()
             pb.Size((tot + 7) // 8 + 2)
             ow = obits.BitWriter((tot + 7) // 8 + 2)
             pb.WriteBits(5, 3)                                 # cursor not byte aligned
             ow.WriteBits(5, 3)
-            for i, w in zip(idx, wid):
-                for v, n in zip(i, w):
-                    if not (sbr and False):
-                        pb.WriteBits(v, n)
-                        ow.WriteBits(v, n)
-            if sbr:
-                continue                                       # SBR streams carry only the last index of omitted bands: covered by the .pac tests
+            for f in sent:
+                for v, n in f:
+                    pb.WriteBits(v, n)
+                    ow.WriteBits(v, n)
             pb.ResetPointers()
             pb.ReadBits(3)
             rd = obits.BitReader(ow.bytes())
             rd.ReadBits(3)
-            y = codec.Decode(None, ba, None, scale, pb, _params(fs, rate, vq, sbr, short), last, cur, nxt)
-            yo = ocodec.decode_channel_vq(rd, ba, scale, po, half, last, cur, nxt)
+            if sbr:                                            # coder/codec.py:95-222
+                y = codec.Decode_SBR(None, ba, None, scale, pb, _params(fs, rate, vq, sbr, short), last, cur, nxt)
+                yo = ocodec.decode_channel_sbr(rd, ba, scale, po, half, last, cur, nxt)
+            else:
+                y = codec.Decode(None, ba, None, scale, pb, _params(fs, rate, vq, sbr, short), last, cur, nxt)
+                yo = ocodec.decode_channel_vq(rd, ba, scale, po, half, last, cur, nxt)
             np.testing.assert_allclose(y, yo, rtol=0, atol=1e-12)
             assert pb.iByte * 8 + pb.iBit == 3 + tot
         else:

@@ -179,3 +179,63 @@ def test_edge_cases_identical_to_reference(rate):
         _, y = opac.decode_pac(ref)
         want = g[f"{name}_{rate}_pcm"]
         assert np.array_equal(y[:, :want.shape[1]], want), name
+
+
+def test_whole_file_goldens_are_consistent():
+    """tests/golden/full_records.npz (made by make_full_golden.py): the oracle's whole-file encodings equal the
+    reference's shipped fixtures record for record, except 4 records of quar48_1 that the reference itself does
+    not reproduce in the build container; the committed glockenspiel streams are the shipped fixtures; the
+    oracle's decode of them equals the unmodified reference decoder's PCM."""
+    import zlib
+    rec = np.load(os.path.join(GOLDEN, "full_records.npz"))
+    md5 = json.load(open(os.path.join(GOLDEN, "full_md5.json")))
+    total = 0
+    for name in ("castanet", "harpsichord", "quar48_1", "spmg"):
+        for rate in (96, 128):
+            tag = f"{name}_{rate}"
+            diff = np.nonzero(rec[tag + "_orc_crc"] != rec[tag + "_fix_crc"])[0].tolist()
+            assert diff == ([978, 979, 1026, 1027] if name == "quar48_1" else []), tag
+            assert np.array_equal(rec[tag + "_orc_len"], rec[tag + "_fix_len"])
+            if not diff:
+                assert md5[f"oracle:{tag}.pac"] == md5[f"{name}_coded_{rate}.pac"]
+            total += len(rec[tag + "_fix_crc"])
+    assert total == 2 * (1726 + 1414 + 1978 + 1812)
+    for rate in (96, 128):
+        buf = open(os.path.join(GOLDEN, f"glockenspiel_coded_{rate}.pac"), "rb").read()
+        assert hashlib.md5(buf).hexdigest() == md5[f"glockenspiel_coded_{rate}.pac"]
+        o, r = rec[f"glockenspiel_{rate}_orc_pcm_crc"], rec[f"glockenspiel_{rate}_ref_pcm_crc"]
+        n = r.shape[1] - 1                                   # the reference's WAV ends inside the last block
+        assert np.array_equal(o[:, :n], r[:, :n])
+    assert zlib.crc32(b"") == 0
+
+
+@pytest.mark.parametrize("rate", [96, 128])
+def test_oracle_reproduces_committed_whole_file_records(rate):
+    """Pins the committed whole-file oracle records (full_records.npz) to the oracle as it runs here: blocks
+    300..311 of castanet re-encoded from the committed PCM (blocks >= 302 of the window see the same prior block
+    and the same three transient flags as in the file; no block before them is dropped, so record 2 b + c is
+    block b, channel c).
+
+    quar48_1's four deviating records (978, 979, 1026, 1027) are NOT reproducible even by the oracle itself: they
+    lie in a stretch of near-silence (samples in {-1, 0}; some blocks -1 throughout), i.e. frames that are one
+    real MDCT line plus ~1000 lines of FFT rounding noise which the reference still quantises.
+    NumPy's pocketfft takes different SIMD paths depending on buffer alignment, so the same code on the same
+    machine codes those records differently from run to run (seen here: a windowed re-encode of that region
+    differs from the whole-file run in one of them).  They are reported as a count, not matched."""
+    import zlib
+    import struct
+    pcm = np.load(os.path.join(GOLDEN, "full_pcm.npz"))
+    rec = np.load(os.path.join(GOLDEN, "full_records.npz"))
+    b0, b1 = 300, 312
+    x = pcm["castanet"][:, b0 * 1024:b1 * 1024]
+    buf = pac.encode_pcm(x, int(pcm["castanet_fs"]), rate)
+    pos, crcs = 30 + 2 * struct.unpack_from("<L", buf, 26)[0], []
+    while pos + 4 <= len(buf):
+        n = struct.unpack_from("<L", buf, pos)[0]
+        crcs.append(zlib.crc32(buf[pos + 4:pos + 4 + n]))
+        pos += 4 + n
+    assert len(crcs) == 2 * (b1 - b0 + 2)
+    want = rec[f"castanet_{rate}_orc_crc"]
+    for j in range(2, b1 - b0):
+        for c in range(2):
+            assert crcs[2 * j + c] == want[2 * (b0 + j) + c], (b0 + j, c)
