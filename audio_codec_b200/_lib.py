@@ -10,7 +10,7 @@ from pathlib import Path
 import numpy as np
 
 _PKG = Path(__file__).resolve().parent
-_LIB_PATH = _PKG / "libpac_b200.so"
+_LIB_PATH = _PKG / os.environ.get("PAC_LIB_NAME", "libpac_b200.so")   # import-time only: kernel experiments (tools/)
 
 F32, F64 = 0, 1
 W_SINE, W_START, W_STOP, W_STARTSTOP, W_KAISER, W_NONE, W_HANN = range(7)
@@ -59,6 +59,7 @@ def _load():
         "pac_transient_detect": (i, [vp, vp, ll, i, i, d, vp, vp]),
         "pac_calc_smr": (i, [vp, i, vp, vp, vp, ll, i, i, pi, pi, vp, vp, vp]),
         "pac_psy_map": (i, [vp, i, vp, ll, vp, vp]),
+        "pac_pcm_to_float": (i, [vp, vp, ll, vp, vp]),
         "pac_bit_alloc": (i, [vp, vp, i, i, pi, vp, ll, vp, vp]),
         "pac_quantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
         "pac_dequantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
@@ -87,7 +88,7 @@ EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_set_option", "pac_g
            "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams", "pac_last_kernel_ms",
            "pac_kernel_stats", "pac_kernel_launches",
            "pac_encode_host", "pac_decode_host",
-           "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_bit_alloc", "pac_quantize_uniform",
+           "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_pcm_to_float", "pac_bit_alloc", "pac_quantize_uniform",
            "pac_dequantize_uniform", "pac_scale_factor", "pac_mantissa", "pac_dequantize", "pac_gain_shape_quantize",
            "pac_gain_shape_dequantize", "pac_pack_bits", "pac_unpack_bits", "pac_record_stride", "pac_encode_blocks",
            "pac_encode_frames", "pac_decode_blocks", "pac_decode_frames"]
@@ -130,7 +131,7 @@ class Context:
         check(lib.pac_create(self.device, C.byref(self.cfg), C.byref(h)))
         self.h = h
 
-    OPTIONS = {"batch_cb": 0, "smem_pad": 1, "host_chunk_mb": 2}
+    OPTIONS = {"batch_cb": 0, "smem_pad": 1, "host_chunk_mb": 2, "variant": 3}
 
     def set_option(self, name, value):
         """Tuning knobs / test hooks (pac_set_option); 0 restores the default."""

@@ -9,7 +9,7 @@ from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
-LIB = PKG / "libpac_b200.so"
+LIB = PKG / os.environ.get("PAC_LIB_NAME", "libpac_b200.so")   # experiments build variants beside the product library
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--use_fast_math=false"]
@@ -34,8 +34,8 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
     objs = []
-    obj_dir = PKG / "build"
-    obj_dir.mkdir(exist_ok=True)
+    obj_dir = PKG / "build" / LIB.stem if LIB.name != "libpac_b200.so" else PKG / "build"
+    obj_dir.mkdir(parents=True, exist_ok=True)
     procs = []
     for src in sources():
         obj = obj_dir / (src.stem + ".o")

@@ -104,7 +104,21 @@ struct EncArgs {
     int* perm;             // [nBatch] dense position -> block of the batch
     int* counts;           // [2] long / transient blocks placed so far
     int cb0, nBatch;
+    const int* wbStream;   // [totWb] stream of every written block (k_wbmap), or nullptr
+    int variant;           // 0: current kernels; other values select the previous forms (A/B measurements, pac_set_option)
 };
+
+// stream index of every written block (one binary search per block here instead of one per channel-block CTA)
+__global__ void k_wbmap(const int* __restrict__ wbOff, int nStreams, int totWb, int* __restrict__ wbStream) {
+    const int wb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (wb >= totWb) return;
+    int lo = 0, hi = nStreams;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (wbOff[mid] <= wb) lo = mid; else hi = mid;
+    }
+    wbStream[wb] = lo;
+}
 
 // FRONT: the batched path (a.pre set): stops after the psychoacoustic model, needs enc_front_smem_bytes()
 // only and runs four CTAs per SM.
@@ -120,14 +134,19 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     S.logVal = nullptr; S.logW = nullptr; S.logCnt = nullptr; S.logCap = 0;
 
     const int tid = threadIdx.x;
+#ifdef PAC_PHASE_TIMING
+    const long long t_k0 = clock64();
+#endif
     const int C = dev->nChannels;
     const int cb = blockIdx.x + a.cb0;        // written channel-block index
     const int wb = cb / C, c = cb - wb * C;   // written block (global), channel
     int lo = 0, hi = a.nStreams;
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (a.wbOff[mid] <= wb) lo = mid; else hi = mid;
-    }
+    if (FRONT && a.wbStream) lo = a.wbStream[wb];            // k_wbmap did the search once per written block
+    else
+        while (hi - lo > 1) {
+            int mid = (lo + hi) >> 1;
+            if (a.wbOff[mid] <= wb) lo = mid; else hi = mid;
+        }
     const int s = lo, j = wb - a.wbOff[s], nbs = a.nb[s];
     const unsigned char* det = a.det + a.blkOff[s];
     // flags (coder/pacfile.py:717-743): written block j carries next = det[j], cur = det[j-1],
@@ -140,6 +159,16 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     const int priorBlk = j == 0 ? -1 : min(j - 1, nbs - 1);
     const short* base = a.pcm + ((long long)a.blkOff[s] * C + (long long)c * nbs) * 1024;
     T* xs = reinterpret_cast<T*>(S.xs);
+    if (FRONT && a.variant == 0 && (((size_t)a.pcm) & 15) == 0) {
+        // eight samples (one 16-byte load) per thread, division-free exact conversion
+        const int i0 = tid * 8;
+        const int blk = i0 < 1024 ? priorBlk : dataBlk;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (blk >= 0) v = __ldg(reinterpret_cast<const uint4*>(base + (long long)blk * 1024 + (i0 & 1023)));
+        const short* sv = reinterpret_cast<const short*>(&v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) xs[i0 + e] = (T)pcm_to_double_fast(sv[e]);
+    } else
     for (int i = tid; i < 2048; i += ENC_NT) {
         int blk = i < 1024 ? priorBlk : dataBlk;
         xs[i] = blk < 0 ? (T)0 : (T)pcm_to_double(base[(long long)blk * 1024 + (i & 1023)]);
@@ -163,9 +192,12 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
         S.misc[3] = bw.pos;
     }
     __syncthreads();
+#ifdef PAC_PHASE_TIMING
+    if (tid == 0) atomicAdd(&g_pac_phase[11 + (cur ? 16 : 0)], (unsigned long long)(clock64() - t_k0));   // prologue: stream search + PCM load
+#endif
     int declared = 4;                         // "+4 for block switching" (pacfile.py:560)
-    EncPreOut po = {nullptr, nullptr, 0};
-    if (FRONT) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); }
+    EncPreOut po = {nullptr, nullptr, 0, 0};
+    if (FRONT) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); po.prune = a.variant == 0; }
     if (!cur) {
         int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
         declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err, po);
@@ -528,6 +560,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     size_t oY = carve((size_t)batchGroups * 32 * EPRE_WS_PER_CB * sizeof(int));
     size_t oWords = carve((size_t)batchGroups * 32 * EPRE_WORDS_PER_CB * sizeof(unsigned));
     size_t oPerm = carve((size_t)(batchCb + 2) * sizeof(int));
+    size_t oWbS = carve((size_t)totWb * sizeof(int));
     void* scr = nullptr;
     if ((rc = pac_scratch(ctx, o, &scr))) return rc;
     unsigned char* sb = (unsigned char*)scr;
@@ -546,6 +579,13 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
     size_t smem = enc_smem_bytes() + (size_t)ctx->optSmemPad;
     a.pre = nullptr; a.preLines = nullptr; a.perm = nullptr; a.counts = nullptr; a.cb0 = 0; a.nBatch = (int)nCh;
+    a.variant = ctx->optVariant;
+    a.wbStream = nullptr;
+    if (vq) {
+        k_wbmap<<<(unsigned)((totWb + 255) / 256), 256, 0, st>>>(dWbOff, S, (int)totWb, (int*)(sb + oWbS));
+        a.wbStream = (int*)(sb + oWbS);
+        ++ctx->launches;
+    }
     const size_t smemF = enc_front_smem_bytes();
     PAC_CHECK(cudaFuncSetAttribute(k_encode<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     PAC_CHECK(cudaFuncSetAttribute(k_encode<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

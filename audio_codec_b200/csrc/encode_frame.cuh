@@ -34,6 +34,18 @@ __device__ __forceinline__ double pcm_to_double(short c) {
     return c < 0 ? -v : v;
 }
 
+// The same value without the division: q0 = x r, one Newton correction with the exact remainder
+// (r = fl(1 / 65535)).  Equal to the correctly rounded x / 65535 for every even x in [0, 65534] (checked
+// exhaustively in exact rational arithmetic, and on the device: tests/test_ops_gpu.py).
+__device__ __forceinline__ double pcm_to_double_fast(short c) {
+    int m = c < 0 ? -(int)c : (int)c;
+    m &= 0x7fff;
+    const double x = (double)(2 * m), r = 1.0 / 65535.0;
+    const double q0 = __dmul_rn(x, r);
+    const double v = fma(fma(-q0, 65535.0, x), r, q0);
+    return c < 0 ? -v : v;
+}
+
 // Batched back end of VQ streams (encode.cu): k_encode stops after the bit allocation and leaves the
 // scaled lines and this header; k_pvq quantises one band per thread; k_pack assembles the record.
 // slot = sub-frame * nBands + band.
@@ -51,7 +63,7 @@ struct EncPre {
     unsigned char pad[2];
     int p;                            // position in the batch's dense order (long blocks from the front, transient from the back)
 };
-struct EncPreOut { EncPre* hdr; double* lines; int sf; };     // lines: this block's column of the interleaved line array
+struct EncPreOut { EncPre* hdr; double* lines; int sf; int prune; };     // prune: band_smr_pruned instead of masked_threshold + band_smr     // lines: this block's column of the interleaved line array
 __device__ __forceinline__ size_t epre_line_index(long long p, int k) {
     return ((size_t)(p >> 5) * 1024 + (size_t)k) * 32 + (size_t)(p & 31);
 }
@@ -394,7 +406,7 @@ static __device__ __noinline__ int encode_back(const PacDev* __restrict__ dev, u
 // path); bit allocation and quantisation are always fp64 + integer.
 template <int N, typename T>
 __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, const T* fx, int shape, bool cur,
-                            bool lastOrNext, bool sbr, int* bpos, int* err, EncPreOut po = {nullptr, nullptr, 0}) {
+                            bool lastOrNext, bool sbr, int* bpos, int* err, EncPreOut po = {nullptr, nullptr, 0, 0}) {
     constexpr int H = N / 2, Q = N / 4;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
@@ -450,9 +462,18 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     PHASE(1);
     // (3) psychoacoustic model -> SMR per band
     const MaskerList<T> ml = masker_list<T>(reinterpret_cast<T*>(S.fb));
-    const int nMask = pick_maskers<N, ENC_NT, T>(mkT, pc, ml, tid);
-    masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mkT, tid);
-    band_smr<ENC_NT, T>(S.lines, scale, mkT, bands, S.smr, tid);
+    const int nMask = po.prune ? pick_maskers<N, ENC_NT, T, true>(mkT, pc, ml, tid) : pick_maskers<N, ENC_NT, T, false>(mkT, pc, ml, tid);
+    PHASE(9);
+    if (po.prune) {
+        // scratch: the frame samples of a long block are dead by now; a short sub-frame (every line exact: no
+        // candidate list) must leave them to its siblings and uses tmp + red (384 bytes)
+        band_smr_pruned<N, ENC_NT, T>(pc, ml, nMask, S.lines, scale, mkT, bands, S.smr,
+                                      N == PAC_NLONG ? (void*)S.xs : (void*)S.tmp, tid);
+    } else {
+        masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mkT, tid);
+        PHASE(10);
+        band_smr<ENC_NT, T>(S.lines, scale, mkT, bands, S.smr, tid);
+    }
 
     PHASE(2);
     const int flags = (N == PAC_NLONG ? 1 : 0) | (sbr ? 2 : 0) | (cur ? 4 : 0) | (lastOrNext ? 8 : 0);

@@ -279,7 +279,8 @@ extern "C" int pac_dequantize(pac_ctx* ctx, int scale, const long long* d_mant, 
 }
 
 // ---------------------------------------------------------------- psychoac.SPL / Intensity / Bark / Thresh
-enum { PSY_SPL = 0, PSY_INTENSITY = 1, PSY_BARK = 2, PSY_THRESH = 3 };
+enum { PSY_SPL = 0, PSY_INTENSITY = 1, PSY_BARK = 2, PSY_THRESH = 3,
+       PSY_SPL_SL = 4, PSY_BARK_SL = 5 };      // the straight-line forms the stream encoder uses (must give the same bits)
 
 __global__ void k_psy_map(int op, const double* __restrict__ x, long long n, double* __restrict__ out) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -290,6 +291,8 @@ __global__ void k_psy_map(int op, const double* __restrict__ x, long long n, dou
             case PSY_SPL: r = spl_of(v); break;                               // coder/psychoac.py:10-25
             case PSY_INTENSITY: r = pow(10.0, (v - 96.0) / 10.0); break;      // :28-32
             case PSY_BARK: r = bark_of(v); break;                             // :43-48
+            case PSY_SPL_SL: r = spl_pn<double>(v); break;
+            case PSY_BARK_SL: r = bark_sl(v); break;
             default: {                                                        // :35-40
                 double f = v < 10.0 ? 10.0 : v;
                 double u = f / 1000.0, d = u - 3.3;
@@ -301,12 +304,31 @@ __global__ void k_psy_map(int op, const double* __restrict__ x, long long n, dou
 }
 
 extern "C" int pac_psy_map(pac_ctx* ctx, int op, const double* d_x, long long n, double* d_out, void* stream) {
-    if (!ctx || op < PSY_SPL || op > PSY_THRESH) return PAC_ERR_ARG;
+    if (!ctx || op < PSY_SPL || op > PSY_BARK_SL) return PAC_ERR_ARG;
     if (n <= 0) return 0;
     if (!d_x || !d_out) return PAC_ERR_ARG;
     PAC_CHECK(cudaSetDevice(ctx->device));
     const int grid = (int)std::min<long long>((n + 255) / 256, 148 * 16);
     k_psy_map<<<grid, 256, 0, (cudaStream_t)stream>>>(op, d_x, n, d_out);
+    OPS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------- pcmfile.PCMFile.ReadDataBlock's sample mapping
+// int16 code -> signed fraction (coder/pcmfile.py:89-98): the division-free form the stream encoder uses
+// (pcm_to_double_fast), exposed so that it can be checked for every code against the division.
+__global__ void k_pcm_to_float(const short* __restrict__ x, long long n, double* __restrict__ out) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = pcm_to_double_fast(x[i]);
+}
+
+extern "C" int pac_pcm_to_float(pac_ctx* ctx, const short* d_pcm, long long n, double* d_out, void* stream) {
+    if (!ctx) return PAC_ERR_ARG;
+    if (n <= 0) return 0;
+    if (!d_pcm || !d_out) return PAC_ERR_ARG;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    const int grid = (int)std::min<long long>((n + 255) / 256, 148 * 16);
+    k_pcm_to_float<<<grid, 256, 0, (cudaStream_t)stream>>>(d_pcm, n, d_out);
     OPS_LAUNCH_CHECK();
     return 0;
 }

@@ -373,6 +373,7 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     c->optBatchCb = 0;
     c->optSmemPad = 0;
     c->optHostChunkMb = 0.0;
+    c->optVariant = 0;
     c->cfg = *cfg;
     c->dev = nullptr;
     c->scratch = nullptr;
@@ -511,6 +512,7 @@ extern "C" int pac_set_option(pac_ctx* c, int option, double value) {
         case PAC_OPT_BATCH_CB: c->optBatchCb = (long long)value; return 0;
         case PAC_OPT_SMEM_PAD: c->optSmemPad = (int)value; return 0;
         case PAC_OPT_HOST_CHUNK_MB: c->optHostChunkMb = value; return 0;
+        case PAC_OPT_VARIANT: c->optVariant = (int)value; return 0;
         default: return PAC_ERR_ARG;
     }
 }

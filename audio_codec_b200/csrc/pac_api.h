@@ -33,6 +33,7 @@ struct pac_ctx {
     long long optBatchCb;    // channel-blocks per batch of the thread-per-band kernels (0: default)
     int optSmemPad;          // extra dynamic shared memory for the frame kernels (occupancy experiments)
     double optHostChunkMb;   // smallest chunk of the host-buffer pipeline, MB of PCM (0: default)
+    int optVariant;          // 0: current kernels; bit flags select earlier forms of a stage (A/B timing, same results)
     // windows of arbitrary length for pac_window, built on demand
     struct WinEntry { int kind, N, Ns; double alpha; const double* d; const float* f; };
     std::vector<WinEntry> winCache;

@@ -305,6 +305,8 @@ def main():
     nbs = [nb] * S
     hdr = [n] * S
     ctx = _lib.Context(sample_rate=FS, n_channels=2, rate_kbps=RATE, device=local)
+    if os.environ.get("PAC_BENCH_VARIANT"):                      # A/B timing of earlier kernel forms (same results)
+        ctx.set_option("variant", int(os.environ["PAC_BENCH_VARIANT"]))
     cap = _lib.lib.pac_encode_bound(ctx.h, (__import__("ctypes").c_int * S)(*nbs), S)
     d_out = torch.empty(int(cap), dtype=torch.uint8, device=dev)
     d_dec = None

@@ -59,7 +59,8 @@ void pac_destroy(pac_ctx* ctx);
  * thread-per-band kernels (default 131072; small values exercise the batch loop).  SMEM_PAD: extra
  * dynamic shared memory of the frame kernels (occupancy experiments).  HOST_CHUNK_MB: smallest chunk
  * (MB of PCM) of the pac_encode_host / pac_decode_host copy pipeline (default 24). */
-enum pac_option { PAC_OPT_BATCH_CB = 0, PAC_OPT_SMEM_PAD = 1, PAC_OPT_HOST_CHUNK_MB = 2 };
+enum pac_option { PAC_OPT_BATCH_CB = 0, PAC_OPT_SMEM_PAD = 1, PAC_OPT_HOST_CHUNK_MB = 2,
+                  PAC_OPT_VARIANT = 3 /* bit flags: run the previous form of a stage (same results; A/B timing, tests) */ };
 int pac_set_option(pac_ctx* ctx, int option, double value);
 const char* pac_strerror(int status);
 /* band layout as ScaleFactorBands(AssignMDCTLinesFromFreqLimits(..)) builds it
@@ -174,8 +175,13 @@ int pac_calc_smr(pac_ctx* ctx, int dtype, const double* d_data, const double* d_
                  void* stream);
 
 /* psychoac.SPL (array form) / Intensity / Bark / Thresh (coder/psychoac.py:10-48), elementwise;
- * op: 0 SPL, 1 Intensity, 2 Bark, 3 Thresh. */
+ * op: 0 SPL, 1 Intensity, 2 Bark, 3 Thresh; 4 / 5: SPL / Bark in the straight-line form the stream encoder
+ * runs (same bits as 0 / 2 for non-negative finite input; tests/test_ops_gpu.py). */
 int pac_psy_map(pac_ctx* ctx, int op, const double* d_x, long long n, double* d_out, void* stream);
+
+/* PCMFile.ReadDataBlock's sample mapping (coder/pcmfile.py:89-98): int16 code -> sign * 2|c| / 65535
+ * (-32768 -> 0.0), elementwise, as the stream encoder applies it. */
+int pac_pcm_to_float(pac_ctx* ctx, const short* d_pcm, long long n, double* d_out, void* stream);
 
 /* bitalloc.BitAlloc(bitBudget, maxMantBits, nBands, nLines, SMR) (coder/bitalloc.py:62-121);
  * BitAlloc_SBR is the same call with nLines[omitted] = 1 (coder/bitalloc.py:123-145). */

@@ -331,3 +331,40 @@ def test_encode_decode_single_channel_matches_oracle(fs, rate, vq, sbr, short):
             y = codec.Decode(sf, ba, mant, scale, None, _params(fs, rate, vq, sbr, short), last, cur, nxt)
             yo = ocodec.decode_channel_bfp(ba, sf, full, scale, po, half, last, cur, nxt)
             np.testing.assert_allclose(y, yo, rtol=0, atol=1e-12)
+
+
+def test_pcm_mapping_exact_for_every_code():
+    """PCMFile.ReadDataBlock's int16 -> fraction mapping (coder/pcmfile.py:89-98) as the stream encoder applies
+    it (multiply + one Newton correction instead of the division): all 65 536 codes equal the oracle's division."""
+    import ctypes as C
+    import torch
+    from audio_codec_b200 import _lib
+    codes = np.arange(-32768, 32768, dtype=np.int16)
+    d = torch.from_numpy(codes).cuda()
+    out = torch.empty(codes.size, dtype=torch.float64, device="cuda")
+    ctx = _lib.default_context(48000)
+    _lib.check(_lib.lib.pac_pcm_to_float(ctx.h, C.c_void_p(d.data_ptr()), codes.size, C.c_void_p(out.data_ptr()),
+                                         _lib.stream_ptr()))
+    assert np.array_equal(out.cpu().numpy(), dsp.pcm_to_float(codes))
+
+
+def test_straight_line_transcendentals_are_bit_identical_to_the_library_calls():
+    """The stream encoder evaluates log10 / atan through straight-line transcriptions of the library's main paths
+    (so that several evaluations interleave).  They must give the library's bits: SPL and Bark through both forms
+    (pac_psy_map ops 0 / 4 and 2 / 5) over 2 M inputs spanning the whole range the codec produces, plus edge values."""
+    import ctypes as C
+    import torch
+    from audio_codec_b200 import _lib
+    rng = np.random.default_rng(99)
+    inten = np.concatenate([10.0 ** rng.uniform(-30, 6, 1 << 20), rng.uniform(0, 4, 1 << 16),
+                            [0.0, 1e-8, 1.0, 2.0, 0.5, 1e-300, 4.0, np.sqrt(2.0), np.nextafter(np.sqrt(2.0), 0), 1e-16]])
+    freq = np.concatenate([rng.uniform(0, 24000, 1 << 20), 10.0 ** rng.uniform(-3, 4.4, 1 << 16),
+                           [0.0, 1315.789, 1315.79, 7500.0, 7499.999999, 24000.0, 1000.0 / 0.76]])
+    ctx = _lib.default_context(48000)
+    for x, a, b in ((inten, _lib.PSY_SPL, 4), (freq, _lib.PSY_BARK, 5)):
+        d = torch.from_numpy(x).cuda()
+        o1, o2 = torch.empty_like(d), torch.empty_like(d)
+        for op, o in ((a, o1), (b, o2)):
+            _lib.check(_lib.lib.pac_psy_map(ctx.h, op, C.c_void_p(d.data_ptr()), d.numel(), C.c_void_p(o.data_ptr()),
+                                            _lib.stream_ptr()))
+        assert torch.equal(o1.view(torch.int64), o2.view(torch.int64)), int((o1 != o2).sum())

@@ -11,7 +11,8 @@ pcm = bench.synth(S, n, 422, "cuda")
 d = torch.zeros((S, 2, nb * 1024), dtype=torch.int16, device="cuda"); d[:, :, :n] = pcm
 ctx = _lib.Context(48000, 2, 128)
 buf = (C.c_ulonglong * 32)()
-names = ["mdct", "hannfft+scale", "psy", "bitalloc", "setup", "pvq plan", "pvq leaves", "header(t0)", "merge"]
+names = ["mdct", "hannfft+scale", "band_smr", "bitalloc", "setup", "pvq plan", "pvq leaves", "header(t0)", "merge", "pick_maskers",
+         "masked_threshold", "prologue(load)"]
 for it in range(2):
     _lib.lib.pac_debug_phases(buf)
     engine.encode_device(ctx, d.reshape(-1), [nb] * S, [n] * S)
