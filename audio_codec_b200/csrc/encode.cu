@@ -105,8 +105,11 @@ struct EncArgs {
     int* counts;           // [2] long / transient blocks placed so far
     int cb0, nBatch;
     const int* wbStream;   // [totWb] stream of every written block (k_wbmap), or nullptr
-    int variant;           // 0: current kernels; other values select the previous forms (A/B measurements, pac_set_option)
+    int variant;           // pac_set_option(PAC_OPT_VARIANT): 0 current kernels; bit 0: the 256-thread k_encode<T, true> front end;
+                           // bit 1: with the exhaustive masked threshold and scalar loads (A/B timing, same results)
 };
+
+#include "encode_front.cuh"     // k_encode_front (needs EncArgs)
 
 // stream index of every written block (one binary search per block here instead of one per channel-block CTA)
 __global__ void k_wbmap(const int* __restrict__ wbOff, int nStreams, int totWb, int* __restrict__ wbStream) {
@@ -159,7 +162,7 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
     const int priorBlk = j == 0 ? -1 : min(j - 1, nbs - 1);
     const short* base = a.pcm + ((long long)a.blkOff[s] * C + (long long)c * nbs) * 1024;
     T* xs = reinterpret_cast<T*>(S.xs);
-    if (FRONT && a.variant == 0 && (((size_t)a.pcm) & 15) == 0) {
+    if (FRONT && !(a.variant & 2) && (((size_t)a.pcm) & 15) == 0) {
         // eight samples (one 16-byte load) per thread, division-free exact conversion
         const int i0 = tid * 8;
         const int blk = i0 < 1024 ? priorBlk : dataBlk;
@@ -197,7 +200,7 @@ k_encode(const PacDev* __restrict__ dev, EncArgs a) {
 #endif
     int declared = 4;                         // "+4 for block switching" (pacfile.py:560)
     EncPreOut po = {nullptr, nullptr, 0, 0};
-    if (FRONT) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); po.prune = a.variant == 0; }
+    if (FRONT) { po.hdr = a.pre + blockIdx.x; po.lines = a.preLines + epre_line_index(S.misc[8], 0); po.prune = !(a.variant & 2); }
     if (!cur) {
         int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
         declared += encode_frame<PAC_NLONG, T>(dev, S, xs, shape, false, last || nxt, dev->useSBR != 0, &S.misc[3], a.err, po);
@@ -591,6 +594,10 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     PAC_CHECK(cudaFuncSetAttribute(k_encode<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     PAC_CHECK(cudaFuncSetAttribute(k_encode<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
     PAC_CHECK(cudaFuncSetAttribute(k_encode<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode_front<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)enf_smem_bytes()));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode_front<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)enf_smem_bytes()));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode_front<float>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    PAC_CHECK(cudaFuncSetAttribute(k_encode_front<double>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     cudaEventRecord(ctx->ev[0], st);
     for (long long q0 = 0; q0 < nCh; q0 += vq ? batchCb : nCh) {
         const long long nq = vq ? std::min(batchCb, nCh - q0) : nCh;
@@ -601,7 +608,10 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
             PAC_CHECK(cudaMemsetAsync(a.counts, 0, 2 * sizeof(int), st));
         }
         pac_kev_begin(ctx, 0, st);
-        if (vq) {
+        if (vq && !(a.variant & 1)) {
+            if (ctx->cfg.precision == PAC_F32) k_encode_front<float><<<(unsigned)nq, ENF_NT, enf_smem_bytes(), st>>>(ctx->dev, a);
+            else k_encode_front<double><<<(unsigned)nq, ENF_NT, enf_smem_bytes(), st>>>(ctx->dev, a);
+        } else if (vq) {
             if (ctx->cfg.precision == PAC_F32) k_encode<float, true><<<(unsigned)nq, ENC_NT, smemF, st>>>(ctx->dev, a);
             else k_encode<double, true><<<(unsigned)nq, ENC_NT, smemF, st>>>(ctx->dev, a);
         } else {
@@ -642,6 +652,13 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
 }
 
 #ifdef PAC_PHASE_TIMING
+// debug: copy and reset the fine-grained counters of the front end ([0..31] long frames, [32..63] short sub-frames)
+extern "C" int pac_debug_phases_front(unsigned long long* h_out) {
+    unsigned long long z[64] = {0};
+    cudaMemcpyFromSymbol(h_out, g_enf_phase, sizeof(z));
+    cudaMemcpyToSymbol(g_enf_phase, z, sizeof(z));
+    return 0;
+}
 // debug: copy and reset the per-phase cycle counters ([0..15] long frames, [16..31] short sub-frames)
 extern "C" int pac_debug_phases(unsigned long long* h_out) {
     unsigned long long z[32] = {0};

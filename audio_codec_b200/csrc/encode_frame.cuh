@@ -465,10 +465,10 @@ __device__ int encode_frame(const PacDev* __restrict__ dev, const EncSmem& S, co
     const int nMask = po.prune ? pick_maskers<N, ENC_NT, T, true>(mkT, pc, ml, tid) : pick_maskers<N, ENC_NT, T, false>(mkT, pc, ml, tid);
     PHASE(9);
     if (po.prune) {
-        // scratch: the frame samples of a long block are dead by now; a short sub-frame (every line exact: no
-        // candidate list) must leave them to its siblings and uses tmp + red (384 bytes)
-        band_smr_pruned<N, ENC_NT, T>(pc, ml, nMask, S.lines, scale, mkT, bands, S.smr,
-                                      N == PAC_NLONG ? (void*)S.xs : (void*)S.tmp, tid);
+        // candidate list: the frame samples of a long block are dead by now; a short sub-frame has every line
+        // exact (no list) and must leave them to its siblings.  Band keys: tmp + red (384 bytes)
+        band_smr_pruned<N, ENC_NT, T>(pc, ml, nMask, S.lines, scale, mkT, bands, S.smr, S.tmp,
+                                      N == PAC_NLONG ? reinterpret_cast<int*>(S.xs) : nullptr, tid);
     } else {
         masked_threshold<N, ENC_NT, T>(pc, ml, nMask, mkT, tid);
         PHASE(10);

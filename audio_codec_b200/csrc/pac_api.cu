@@ -407,6 +407,14 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     if (!rc) rc = make_numeric_tables<float>(c, &h.f);
     if (!rc) rc = make_psy(c, PAC_HALF_LONG, &h.barkLong, &h.threshLong, &h.fftFreqLong, &h.fftNormLong);
     if (!rc) rc = make_psy(c, PAC_HALF_SHORT, &h.barkShort, &h.threshShort, &h.fftFreqShort, &h.fftNormShort);
+    for (int w = 0; w < 2 && !rc; ++w) {          // band of every MDCT line
+        const PacBands& bd = w ? h.shortBands : h.longBands;
+        std::vector<unsigned char> lb(w ? PAC_HALF_SHORT : PAC_HALF_LONG, 0);
+        for (int b = 0; b < bd.nBands; ++b)
+            for (int i = 0; i < bd.nLines[b]; ++i)
+                if (bd.lower[b] + i < (int)lb.size()) lb[bd.lower[b] + i] = (unsigned char)b;
+        rc = upload(c, lb, w ? &h.lineBandShort : &h.lineBandLong);
+    }
     if (!rc) rc = make_pvq(c);
     if (!rc) rc = make_sbr(c);
     if (!rc) rc = make_theta(c);

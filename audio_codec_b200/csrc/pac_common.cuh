@@ -63,6 +63,8 @@ struct PacDev {
     const double* threshShort; // [128]
     const double* fftFreqLong; // [1025] rfftfreq
     const double* fftFreqShort;// [129]
+    const unsigned char* lineBandLong;   // [1024] band of each MDCT line
+    const unsigned char* lineBandShort;  // [128]
     double fftNormLong;        // 4/(N^2 mean(hanning(N)^2))
     double fftNormShort;
     // PVQ codebook sizes N(L,K), rows L = 0..PAC_PVQ_LMAX, each row up to the first

@@ -2,7 +2,7 @@
 # A/B: new front end (variant 0) against the previous one (variant 1); phase shares of the new one
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; tail -8 gpurun_out/pytest_gpu.log
-for v in 0 1; do
+for v in 0 1 3; do
 PAC_BENCH_VARIANT=$v python bench.py --no-cpu --no-mdct --no-fp32 --steps 5 --warmup 3 > gpurun_out/bench_v$v.json 2> gpurun_out/bench_v$v.err
 python - <<PY
 import json
