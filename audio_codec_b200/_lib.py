@@ -68,6 +68,8 @@ def _load():
         "pac_dequantize": (i, [vp, i, vp, ll, i, i, vp, vp]),
         "pac_gain_shape_quantize": (i, [vp, vp, i, ll, vp, i, vp, vp, vp, i, pi, vp]),
         "pac_gain_shape_dequantize": (i, [vp, vp, ll, vp, vp, i, ll, vp, vp, pi, vp]),
+        "pac_gain_shape_dequantize_static": (i, [vp, vp, ll, vp, vp, i, ll, vp, vp, pi, vp]),
+        "pac_gain_shape_dequantize_static_max_vectors": (ll, [i]),
         "pac_pack_bits": (i, [vp, vp, vp, vp, i, ll, i, vp, pi, vp]),
         "pac_unpack_bits": (i, [vp, vp, i, vp, vp, vp, i, ll, vp, vp]),
         "pac_record_stride": (i, []),
@@ -90,7 +92,8 @@ EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_set_option", "pac_g
            "pac_encode_host", "pac_decode_host",
            "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_pcm_to_float", "pac_bit_alloc", "pac_quantize_uniform",
            "pac_dequantize_uniform", "pac_scale_factor", "pac_mantissa", "pac_dequantize", "pac_gain_shape_quantize",
-           "pac_gain_shape_dequantize", "pac_pack_bits", "pac_unpack_bits", "pac_record_stride", "pac_encode_blocks",
+           "pac_gain_shape_dequantize", "pac_gain_shape_dequantize_static", "pac_gain_shape_dequantize_static_max_vectors",
+           "pac_pack_bits", "pac_unpack_bits", "pac_record_stride", "pac_encode_blocks",
            "pac_encode_frames", "pac_decode_blocks", "pac_decode_frames"]
 
 

@@ -448,6 +448,80 @@ extern "C" int pac_gain_shape_dequantize(pac_ctx* ctx, const unsigned char* d_by
     return err ? PAC_ERR_SOFT : 0;
 }
 
+// ---- no-allocation variant of pac_gain_shape_dequantize (no counterpart in the reference: added
+// for callers that cannot call cudaMalloc - CUDA graph capture, tight serving loops).
+// k_gs_dequantize keeps its three per-vector workspaces in dynamic shared memory and its soft-error word in the
+// context's cudaMalloc'ed scratch; this variant keeps both in ONE file-scope device array of fixed size, so the
+// entry point allocates nothing.  Every GPU that loads the library holds the array (4 MiB + 256 B) until exit.
+// Layout: [0, 256) the soft-error word (cleared by every call), then n_vec x 3 x cap doubles of workspace
+// (written before they are read: nothing else needs clearing).  Every call shares the array: calls that overlap
+// on the GPU (different streams, threads or contexts of one device) race.
+#define PAC_GS_STATIC_WS_BYTES (4u << 20)
+#define PAC_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) unsigned char g_gs_static[256 + PAC_GS_STATIC_WS_BYTES];
+// In host code `g_gs_static` is a host-side stand-in, not a device address: the device address of each GPU's copy
+// is looked up once per device, with that device current, and that pointer is what the kernel receives.
+static unsigned char* s_gs_static_ptr[PAC_STATIC_MAX_DEVICES];
+
+int pac_ops_static_setup(int device) {          // pac_create calls this with `device` current
+    if (device < 0 || device >= PAC_STATIC_MAX_DEVICES) return 0;      // such a device has no no-allocation path
+    if (s_gs_static_ptr[device]) return 0;
+    void* p = nullptr;
+    PAC_CHECK(cudaGetSymbolAddress(&p, g_gs_static));
+    s_gs_static_ptr[device] = (unsigned char*)p;
+    return 0;
+}
+
+__global__ void __launch_bounds__(32)
+k_gs_dequantize_static(const PacDev* __restrict__ dev, const unsigned char* __restrict__ bytes, long long nBits,
+                       const long long* __restrict__ bitpos, const int* __restrict__ budget, int L, int cap,
+                       double* __restrict__ out, long long* __restrict__ posOut, unsigned char* __restrict__ scratch) {
+    int* err = reinterpret_cast<int*>(scratch);
+    double* wsA = reinterpret_cast<double*>(scratch + 256) + (size_t)blockIdx.x * 3 * cap;
+    double* wsB = wsA + cap;
+    double* res = wsB + cap;
+    const long long v = blockIdx.x;
+    const int lane = threadIdx.x;
+    PvqTab pt = {dev->pvqN, dev->pvqRowOff, dev->log2tab, dev->pvqKW, nullptr};
+    BitR br = {bytes, bitpos[v], nBits, 0};
+    int werr = 0;
+    warp_dequantize_gain_shape(pt, br, budget[v], L, wsA, wsB, cap, res, &werr);
+    __syncwarp();
+    for (int i = lane; i < L; i += 32) out[v * L + i] = res[i];
+    if (lane == 0) {
+        posOut[v] = br.pos;
+        if (br.pos > nBits) werr |= PVQ_ERR_STACK;
+        if (werr) atomicOr(err, werr);
+    }
+}
+
+extern "C" long long pac_gain_shape_dequantize_static_max_vectors(int L) {
+    if (L < 1 || L > PAC_PVQ_LMAX) return 0;
+    return (long long)(PAC_GS_STATIC_WS_BYTES / ((size_t)3 * pow2_cap(L) * sizeof(double)));
+}
+
+extern "C" int pac_gain_shape_dequantize_static(pac_ctx* ctx, const unsigned char* d_bytes, long long n_bytes,
+                                                const long long* d_bitpos, const int* d_bit_alloc, int L, long long n_vec,
+                                                double* d_out, long long* d_bitpos_out, int* h_err, void* stream) {
+    if (!ctx || L < 1 || L > PAC_PVQ_LMAX) return PAC_ERR_ARG;
+    if (n_vec <= 0) return 0;
+    if (!d_bytes || !d_bitpos || !d_bit_alloc || !d_out || !d_bitpos_out) return PAC_ERR_ARG;
+    if (n_vec > pac_gain_shape_dequantize_static_max_vectors(L)) return PAC_ERR_TOO_LARGE;
+    if (ctx->device < 0 || ctx->device >= PAC_STATIC_MAX_DEVICES || !s_gs_static_ptr[ctx->device]) return PAC_ERR_UNSUPPORTED;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* scr = s_gs_static_ptr[ctx->device];
+    PAC_CHECK(cudaMemsetAsync(scr, 0, sizeof(int), st));
+    k_gs_dequantize_static<<<(unsigned)n_vec, 32, 0, st>>>(ctx->dev, d_bytes, n_bytes * 8, d_bitpos, d_bit_alloc, L,
+                                                           pow2_cap(L), d_out, d_bitpos_out, scr);
+    OPS_LAUNCH_CHECK();
+    int err = 0;
+    PAC_CHECK(cudaMemcpyAsync(&err, scr, sizeof(int), cudaMemcpyDeviceToHost, st));
+    PAC_CHECK(cudaStreamSynchronize(st));
+    if (h_err) *h_err = err;
+    return err ? PAC_ERR_SOFT : 0;
+}
+
 // ---------------------------------------------------------------- bitpack.PackedBits
 // One warp per row: exclusive scan of the field widths, then every lane writes its
 // fields MSB-first at their bit offsets (coder/bitpack.py:37-102).  Rows are

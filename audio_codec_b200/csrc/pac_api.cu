@@ -418,6 +418,7 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     if (!rc) rc = make_pvq(c);
     if (!rc) rc = make_sbr(c);
     if (!rc) rc = make_theta(c);
+    if (!rc) rc = pac_ops_static_setup(device);     // this device is current (cudaSetDevice above)
     if (!rc) {
         void* d = nullptr;
         if (cudaMalloc(&d, sizeof(PacDev)) != cudaSuccess) rc = PAC_ERR_ALLOC;
@@ -496,6 +497,7 @@ extern "C" const char* pac_strerror(int s) {
         case PAC_ERR_ALLOC: return "allocation failed";
         case PAC_ERR_UNSUPPORTED: return "unsupported configuration (undefined in the reference)";
         case PAC_ERR_SOFT: return "per-frame soft error flagged on device";
+        case PAC_ERR_TOO_LARGE: return "request exceeds the fixed static scratch of a no-allocation entry point";
         default:
             if (s <= -1000) return cudaGetErrorString((cudaError_t)(-s - 1000));
             return "unknown";

@@ -49,6 +49,8 @@ static inline void pac_kev_end(pac_ctx* c, int kind, cudaStream_t st) {
     ++c->launches;
 }
 int pac_scratch(pac_ctx* ctx, size_t bytes, void** out);
+// ops.cu: device address of the static scratch of the no-allocation entry point, once per device (`device` current)
+int pac_ops_static_setup(int device);
 int pac_pinned(pac_ctx* ctx, size_t bytes, void** out);
 int pac_io(pac_ctx* ctx, int which, size_t bytes, void** out);
 // window table of length N (kind: PAC_W_*, Ns = short length for the Edler shapes)

@@ -26,7 +26,8 @@ enum pac_status {
     PAC_ERR_ARG = -1,        /* bad argument */
     PAC_ERR_ALLOC = -2,      /* device/host allocation failed */
     PAC_ERR_UNSUPPORTED = -3,/* e.g. block floating point + SBR (crashes in the reference too) */
-    PAC_ERR_SOFT = -4        /* per-frame soft error flagged on device (see pac_encode flags) */
+    PAC_ERR_SOFT = -4,       /* per-frame soft error flagged on device (see pac_encode flags) */
+    PAC_ERR_TOO_LARGE = -5   /* a *_static (no-allocation) entry point was asked for more than its fixed scratch holds */
     /* <= -1000: -(cudaError_t) - 1000 */
 };
 /* window shapes: coder/window.py:14 SineWindow, :61 StartWindow, :73 StopWindow,
@@ -212,6 +213,19 @@ int pac_gain_shape_quantize(pac_ctx* ctx, const double* d_x, int L, long long n_
 int pac_gain_shape_dequantize(pac_ctx* ctx, const unsigned char* d_bytes, long long n_bytes, const long long* d_bitpos,
                               const int* d_bit_alloc, int L, long long n_vec, double* d_out, long long* d_bitpos_out,
                               int* h_err, void* stream);
+/* NO COUNTERPART IN THE REFERENCE.  pac_gain_shape_dequantize for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it): same arguments, same results, but it calls no cudaMalloc / cudaFree or any allocating routine.  Its
+ * workspaces (3 x pow2ceil(L) doubles per vector) and its soft-error word live in one file-scope device array of
+ * 4 MiB + 256 B that every GPU loading the library holds until exit; its device address is resolved at
+ * pac_create, once per device.  Limit: n_vec <= pac_gain_shape_dequantize_static_max_vectors(L)
+ * (= 4 MiB / (24 * pow2ceil(L)): 341 vectors at L = 363, 174 762 at L = 1); beyond it the call returns
+ * PAC_ERR_TOO_LARGE and does nothing.  All calls on a device share the array: calls that overlap on the GPU
+ * (other streams, threads or contexts) race.  Synchronises `stream`. */
+long long pac_gain_shape_dequantize_static_max_vectors(int L);
+int pac_gain_shape_dequantize_static(pac_ctx* ctx, const unsigned char* d_bytes, long long n_bytes,
+                                     const long long* d_bitpos, const int* d_bit_alloc, int L, long long n_vec,
+                                     double* d_out, long long* d_bitpos_out, int* h_err, void* stream);
 
 /* bitpack.PackedBits.WriteBits / ReadBits (coder/bitpack.py:37-175): row r packs its
  * d_count[r] fields (value, width <= 64) MSB-first into row_bytes bytes (multiple of 4). */
