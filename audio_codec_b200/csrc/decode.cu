@@ -104,7 +104,8 @@ __device__ __forceinline__ BitR rec_reader(const DecArgs& a, long long cb, int* 
     BitR br = {al, bit0, bit0 + 8LL * nBytes, 0};
     const long long room = (a.buf + a.bufBytes) - al;         // readable bytes from the aligned base
     br.cap = (int)min((long long)(DEC_REC_MAX + 16), room & ~7LL);
-    if (br.cap < (int)(ad & 7ull) + nBytes) {                 // the record ends inside the buffer's last partial word
+    if (br.cap < (int)(ad & 7ull) + nBytes || al < a.buf) {   // the record ends inside the buffer's last partial word, or the
+                                                              // aligned base lies before the caller's buffer: byte reads only
         br.p = rec; br.end = 8LL * nBytes; br.cap = 0; bit0 = 0; br.pos = 0;
     }
     *nBytesOut = nBytes;

@@ -61,15 +61,46 @@ def encode_streams(ctx, pcm_list, hdr_samples=None):
 
 
 def parse_header(buf):
-    """coder/pacfile.py:136-151 -> dict of the header fields."""
+    """coder/pacfile.py:136-151 -> dict of the header fields.  Besides master's layout (8 fields: ..., useSBR,
+    useVQ) the two older generations whose files the reference ships are recognised (README.md:4-5 names the
+    branches): 7 fields (test_decoded/: no useVQ field - block floating point with block switching, 18 merged
+    bands) and 6 fields (test_decoded96/, test_decoded_vq/: neither flag, the 25 unmerged Zwicker bands).  "layout"
+    is the number of fields, "header_bytes" the size of the header."""
     import struct
     if buf[:4] != b"PAC ":
         raise RuntimeError("Tried to read a non-PAC file into a PACFile object")
-    fs, C_, ns, nl, nsb, nmsb, sbr, vq = struct.unpack_from("<LHLLHHHH", buf, 4)
-    nb = struct.unpack_from("<L", buf, 26)[0]
-    lines = struct.unpack_from("<%dH" % nb, buf, 30)
-    return dict(sample_rate=fs, n_channels=C_, num_samples=ns, n_mdct_lines=nl, n_scale_bits=nsb,
-                n_mant_size_bits=nmsb, use_sbr=bool(sbr), use_vq=bool(vq), n_lines=lines)
+    fs, C_, ns, nl, nsb, nmsb = struct.unpack_from("<LHLLHH", buf, 4)
+    # a layout is recognised by a band table whose line counts add up to nMDCTLines; a file in which no layout
+    # does is read as master's (its band table is then refused by context_for_header)
+    for layout, extra, strict in ((8, 2, True), (7, 1, True), (6, 0, True), (8, 2, False)):
+        o = 22 + 2 * extra
+        if len(buf) < o + 4:
+            continue
+        nb = struct.unpack_from("<L", buf, o)[0]
+        if not 1 <= nb <= 64 or len(buf) < o + 4 + 2 * nb:
+            continue
+        lines = struct.unpack_from("<%dH" % nb, buf, o + 4)
+        if strict and sum(lines) != nl:
+            continue
+        fl = struct.unpack_from("<%dH" % extra, buf, 22) if extra else ()
+        return dict(sample_rate=fs, n_channels=C_, num_samples=ns, n_mdct_lines=nl, n_scale_bits=nsb,
+                    n_mant_size_bits=nmsb, use_sbr=bool(fl[0]) if extra >= 1 else False,
+                    use_vq=bool(fl[1]) if extra >= 2 else False, n_lines=lines, layout=layout, header_bytes=o + 4 + 2 * nb)
+    raise RuntimeError("unrecognised .pac header layout")
+
+
+def upgrade_legacy_stream(buf):
+    """A 7-field stream (test_decoded/ generation) in master's layout: the same records behind a header with the
+    useVQ field added (= 0: block floating point).  The 6-field generation is refused: its 25-band payload was
+    written by code that is not in the checkout and does not parse as either of master's two quantisers
+    (DESIGN.md 6.1 #4)."""
+    h = parse_header(buf)
+    if h["layout"] == 8:
+        return buf
+    if h["layout"] == 6:
+        raise _lib.PacError("6-field .pac generation (25 unmerged bands, test_decoded96/ and test_decoded_vq/): unsupported, "
+                            "its writer is not in the reference checkout")
+    return bytes(buf[:24]) + b"\0\0" + bytes(buf[24:])
 
 
 def context_for_header(h, precision="f64"):
@@ -104,7 +135,7 @@ def block_records(buf):
     length prefix, coder/pacfile.py:239-256).  Host helper for comparing two encodings."""
     import struct
     h = parse_header(buf)
-    pos = 30 + 2 * len(h["n_lines"])
+    pos = h["header_bytes"]
     out = []
     while pos + 4 <= len(buf):
         n = struct.unpack_from("<L", buf, pos)[0]
@@ -127,7 +158,7 @@ def check_same_configuration(pac_list):
     h = parse_header(pac_list[0])
     for i, b in enumerate(pac_list[1:], 1):
         g = parse_header(b)
-        bad = [k for k in h if k != "num_samples" and h[k] != g[k]]
+        bad = [k for k in h if k not in ("num_samples", "layout", "header_bytes") and h[k] != g[k]]
         if bad:
             raise _lib.PacError(f"stream {i} differs from stream 0 in {', '.join(bad)}: decode streams of "
                                 "different configurations in separate calls")
@@ -136,6 +167,7 @@ def check_same_configuration(pac_list):
 
 def decode_streams(pac_list, precision="f64", ctx=None):
     """Host convenience: list of .pac bytes (same configuration) -> list of int16 [C, n]."""
+    pac_list = [upgrade_legacy_stream(b) for b in pac_list]          # older header generations -> master's layout
     h = check_same_configuration(pac_list)
     if ctx is None:
         ctx = context_for_header(h, precision)

@@ -26,13 +26,17 @@ class PACFile(AudioFile):
 
     # ------------------------------------------------------------------ headers
     def ReadFileHeader(self):
-        """(coder/pacfile.py:136-175)"""
-        if self.fp.read(4) != self.tag:
-            raise RuntimeError("Tried to read a non-PAC file into a PACFile object")
-        fs, nCh, numSamples, nMDCTLines, nScaleBits, nMantSizeBits, useSBR, useVQ = \
-            unpack("<LHLLHHHH", self.fp.read(calcsize("<LHLLHHHH")))
-        nBands = unpack("<L", self.fp.read(4))[0]
-        nLines = unpack("<%dH" % nBands, self.fp.read(2 * nBands))
+        """(coder/pacfile.py:136-175); also the 7-field header of the test_decoded/ generation (no useVQ field:
+        block floating point), see engine.parse_header."""
+        start = self.fp.tell()
+        raw = self.fp.read(4 + 18 + 4 + 4 + 2 * 64)
+        h = engine.parse_header(raw)
+        if h["layout"] == 6:
+            engine.upgrade_legacy_stream(raw)         # raises: unsupported generation
+        self.fp.seek(start + h["header_bytes"])
+        fs, nCh, numSamples, nMDCTLines = h["sample_rate"], h["n_channels"], h["num_samples"], h["n_mdct_lines"]
+        nScaleBits, nMantSizeBits, useSBR, useVQ, nLines = (h["n_scale_bits"], h["n_mant_size_bits"], h["use_sbr"],
+                                                            h["use_vq"], h["n_lines"])
         p = CodingParams()
         p.sampleRate, p.nChannels, p.numSamples = fs, nCh, numSamples
         p.nMDCTLines = p.nSamplesPerBlock = nMDCTLines

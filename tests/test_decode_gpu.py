@@ -69,3 +69,43 @@ def test_mixed_configurations_in_one_call_are_refused():
     bad[18] = 6                                                            # nScaleBits = 6: unsupported by the device quantisers
     with pytest.raises(_lib.PacError, match="unsupported"):
         engine.decode_streams([bytes(bad)])
+
+
+def test_legacy_seven_field_generation_decodes_to_the_reference_wav(tmp_path):
+    """the reference ships files of older bitstream generations (README.md:4-5).  The 7-field
+    header generation (test_decoded/: no useVQ field; block floating point with block switching, nMantSizeBits = 16)
+    decodes bit-exactly to the .wav that sits beside it in the reference: first 60 blocks of
+    test_decoded/castanet_coded_128.pac against the first 61 440 samples of test_decoded/castanet_128.wav, through
+    the batched decoder and through the PACFile block API.  The 6-field generation (25 unmerged bands) is refused."""
+    from audio_codec_b200 import _lib, engine, pacfile
+    buf = open(os.path.join(GOLDEN, "legacy7_castanet_128.pac"), "rb").read()
+    want = np.load(os.path.join(GOLDEN, "legacy7_castanet_128_pcm.npz"))["pcm"]
+    h = engine.parse_header(buf)
+    assert h["layout"] == 7 and not h["use_vq"] and not h["use_sbr"] and h["n_mant_size_bits"] == 16 and len(h["n_lines"]) == 18
+    y = engine.decode_streams([buf])[0]
+    assert y.shape[1] >= want.shape[1] and np.array_equal(y[:, :want.shape[1]], want)
+    # block API: the reference's decode loop (coder/pacfile.py:758-776) on the drop-in classes
+    from audio_codec_b200.pcmfile import PCMFile
+    src = tmp_path / "legacy.pac"
+    src.write_bytes(buf)
+    inF, outF = pacfile.PACFile(str(src)), PCMFile(str(tmp_path / "legacy.wav"))
+    cp = inF.OpenForReading()
+    cp.bitsPerSample = 16
+    cp.numSamples = want.shape[1]
+    outF.OpenForWriting(cp)
+    while True:
+        data = inF.ReadDataBlock(cp)
+        if not data:
+            break
+        outF.WriteDataBlock(data, cp)
+    inF.Close(cp)
+    outF.Close(cp)
+    import wave
+    with wave.open(str(tmp_path / "legacy.wav")) as w:
+        z = np.frombuffer(w.readframes(w.getnframes()), dtype="<i2").reshape(-1, 2).T
+    assert np.array_equal(z[:, :want.shape[1]], want)
+    six = buf[:22] + (25).to_bytes(4, "little") + b"".join(int(v).to_bytes(2, "little") for v in
+          (5, 4, 5, 5, 5, 5, 7, 7, 7, 9, 10, 11, 13, 15, 17, 21, 26, 32, 42, 51, 61, 83, 116, 163, 304)) + b"\0" * 64
+    assert engine.parse_header(six)["layout"] == 6
+    with pytest.raises(_lib.PacError, match="6-field"):
+        engine.decode_streams([six])
