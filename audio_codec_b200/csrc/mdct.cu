@@ -5,6 +5,7 @@
 #include <algorithm>
 #include "mdct.cuh"
 #include "mdct_stream.cuh"
+#include "mdct_tma.cuh"
 #include "pac_api.h"
 
 // ---------------------------------------------------------------- forward
@@ -182,6 +183,20 @@ static int launch_fwd_stream(pac_ctx* ctx, const void* x, long long rowStride, i
     const int grid = (int)std::min<long long>(148, (units + W - 1) / W);
     const int vec = aligned16(x) && aligned16(coefs) && (rowStride * sizeof(T)) % 16 == 0;
     const bool sym = window == PAC_WIN_SINE || window == PAC_WIN_KAISER || window == PAC_WIN_NONE;
+    if (vec && !(ctx->optVariant & 8)) {             // bulk-copy (TMA) pipeline; pac_set_option variant bit 3: the LDG / STG one
+        constexpr int WT = MtCfg<T>::WARPS;
+        const int segT = stream_seg(nRows, nFrames, WT), segsT = (nFrames + segT - 1) / segT;
+        const long long unitsT = (long long)nRows * segsT;
+        const int gridT = (int)std::min<long long>(148, (unitsT + WT - 1) / WT);
+        auto kt = sym ? k_mdct_fwd_tma<T, true> : k_mdct_fwd_tma<T, false>;
+        const size_t smemT = mt_smem_bytes<T>();
+        PAC_CHECK(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemT));
+        kt<<<gridT, WT * 32, smemT, st>>>((const T*)x, rowStride, nFrames, segT, segsT, unitsT, win,
+                                           reinterpret_cast<const cplx<T>*>(t.tw_mdct_long),
+                                           reinterpret_cast<const cplx<T>*>(t.tw_fft[2]), (T*)coefs);
+        PAC_CHECK(cudaGetLastError());
+        return 0;
+    }
     auto kern = sym ? k_mdct_fwd_stream<T, true> : k_mdct_fwd_stream<T, false>;
     const size_t smem = ms_smem_bytes<T>();
     PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -202,6 +217,20 @@ static int launch_inv_stream(pac_ctx* ctx, const void* X, int nRows, int nFrames
     const long long units = (long long)nRows * segs;
     const int grid = (int)std::min<long long>(148, (units + W - 1) / W);
     const int vec = aligned16(X) && aligned16(y) && (rowStride * sizeof(T)) % 16 == 0;
+    if (vec && !(ctx->optVariant & 8)) {             // bulk-copy (TMA) input pipeline
+        constexpr int WT = MtCfg<T>::WARPS;
+        const int segT = stream_seg(nRows, nFrames + 1, WT), segsT = (nFrames + 1 + segT - 1) / segT;
+        const long long unitsT = (long long)nRows * segsT;
+        const int gridT = (int)std::min<long long>(148, (unitsT + WT - 1) / WT);
+        auto kt = k_imdct_ola_tma<T>;
+        const size_t smemT = mt_smem_bytes<T>();
+        PAC_CHECK(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemT));
+        kt<<<gridT, WT * 32, smemT, st>>>((const T*)X, nFrames, segT, segsT, unitsT, win,
+                                           reinterpret_cast<const cplx<T>*>(t.tw_mdct_long),
+                                           reinterpret_cast<const cplx<T>*>(t.tw_fft[2]), (T*)y, rowStride);
+        PAC_CHECK(cudaGetLastError());
+        return 0;
+    }
     auto kern = k_imdct_ola_stream<T>;
     const size_t smem = ms_inv_smem_bytes<T>();
     PAC_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -8,6 +8,7 @@ def run(F=1 << 20, dtype=torch.float32, window=_lib.W_SINE, iters=5):
     g = torch.Generator(device="cuda").manual_seed(422)
     x = (0.25 * torch.randn((2, (F + 1) * 1024), generator=g, device="cuda", dtype=torch.float32)).clamp_(-1, 1).to(dtype)
     ctx = _lib.default_context()
+    ctx.set_option("variant", int(os.environ.get("PAC_BENCH_VARIANT", 0)))
     X = mdct.mdct_frames(x, 2048, window, ctx); y = mdct.imdct_ola(X, 2048, window, ctx)
     torch.cuda.synchronize()
     e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
