@@ -60,6 +60,7 @@ def _load():
         "pac_calc_smr": (i, [vp, i, vp, vp, vp, ll, i, i, pi, pi, vp, vp, vp]),
         "pac_psy_map": (i, [vp, i, vp, ll, vp, vp]),
         "pac_pcm_to_float": (i, [vp, vp, ll, vp, vp]),
+        "pac_selftest_division": (ll, [vp, ll, C.c_ulonglong, vp]),
         "pac_bit_alloc": (i, [vp, vp, i, i, pi, vp, ll, vp, vp]),
         "pac_quantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
         "pac_dequantize_uniform": (i, [vp, vp, ll, i, vp, vp]),
@@ -90,7 +91,7 @@ EXPORTS = ["pac_create", "pac_destroy", "pac_strerror", "pac_set_option", "pac_g
            "pac_header_bytes", "pac_encode_bound", "pac_encode_streams", "pac_decode_plan", "pac_decode_streams", "pac_last_kernel_ms",
            "pac_kernel_stats", "pac_kernel_launches",
            "pac_encode_host", "pac_decode_host",
-           "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_pcm_to_float", "pac_bit_alloc", "pac_quantize_uniform",
+           "pac_window", "pac_transient_detect", "pac_calc_smr", "pac_psy_map", "pac_pcm_to_float", "pac_selftest_division", "pac_bit_alloc", "pac_quantize_uniform",
            "pac_dequantize_uniform", "pac_scale_factor", "pac_mantissa", "pac_dequantize", "pac_gain_shape_quantize",
            "pac_gain_shape_dequantize", "pac_gain_shape_dequantize_static", "pac_gain_shape_dequantize_static_max_vectors",
            "pac_pack_bits", "pac_unpack_bits", "pac_record_stride", "pac_encode_blocks",

@@ -333,6 +333,50 @@ extern "C" int pac_pcm_to_float(pac_ctx* ctx, const short* d_pcm, long long n, d
     return 0;
 }
 
+// ---------------------------------------------------------------- self-test of pac_div (pac_common.cuh)
+// n pseudo-random (x, d) pairs per magnitude class: quotients of the kinds the quantisers form (|x| <= d, d a norm in
+// (0, 4]; also wide exponent ranges).  Counts the pairs for which pac_div differs from the IEEE division.
+__global__ void k_div_selftest(long long n, unsigned long long seed, unsigned long long* __restrict__ bad) {
+    unsigned long long cnt = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        unsigned long long h = (unsigned long long)i * 0x9E3779B97F4A7C15ull + seed;
+        h ^= h >> 31; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 29; h *= 0x94D049BB133111EBull; h ^= h >> 32;
+        unsigned long long g = h * 0xD6E8FEB86659FD93ull + 0x2545F4914F6CDD1Dull;
+        g ^= g >> 33;
+        const int cls = (int)(i & 3);
+        // mantissas from the hash; exponents by class
+        double d = __longlong_as_double((long long)((h & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull));      // [1, 2)
+        double x = __longlong_as_double((long long)((g & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull));
+        const int ed = cls == 0 ? -(int)((h >> 52) & 15) : cls == 1 ? 1 - (int)((h >> 52) & 63) : cls == 2 ? 0 : 200 - (int)((h >> 52) & 511);
+        const int ex = cls == 3 ? 100 - (int)((g >> 52) & 255) : ed - (int)((g >> 52) & 63);
+        d = ldexp(d, ed);
+        x = ldexp(x, ex);
+        if (g >> 63) x = -x;
+        if (cls == 2 && ((g >> 58) & 31) == 0) x = d;                 // the exact quotient 1
+        const PacDiv b = pac_div_by(d);
+        if (__double_as_longlong(pac_div(x, b)) != __double_as_longlong(x / d)) ++cnt;
+        const PacDiv r2 = {__longlong_as_double(0x3FF6A09E667F3BCDLL), __longlong_as_double(0x3FE6A09E667F3BCCLL)};
+        if (__double_as_longlong(pac_div(x, r2)) != __double_as_longlong(x / sqrt(2.0))) ++cnt;
+    }
+    if (cnt) atomicAdd(bad, cnt);
+}
+
+extern "C" long long pac_selftest_division(pac_ctx* ctx, long long n_pairs, unsigned long long seed, void* stream) {
+    if (!ctx || n_pairs <= 0) return PAC_ERR_ARG;
+    PAC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    void* scr = nullptr;
+    int rc = pac_scratch(ctx, 256, &scr);
+    if (rc) return rc;
+    PAC_CHECK(cudaMemsetAsync(scr, 0, 8, st));
+    k_div_selftest<<<148 * 8, 256, 0, st>>>(n_pairs, seed, (unsigned long long*)scr);
+    OPS_LAUNCH_CHECK();
+    unsigned long long bad = 0;
+    PAC_CHECK(cudaMemcpyAsync(&bad, scr, 8, cudaMemcpyDeviceToHost, st));
+    PAC_CHECK(cudaStreamSynchronize(st));
+    return (long long)bad;
+}
+
 // ---------------------------------------------------------------- gain_shape_quantize.*
 static int pow2_cap(int L) {
     int c = 1;

@@ -354,9 +354,10 @@ __device__ __forceinline__ unsigned long long thread_quantize_pvq(const PvqTab& 
     const double l1 = np_abs_sum<XS>(vec, n);
     if (l1 == 0.0) { *err |= PVQ_ERR_DEGENERATE; return 0ull; }
     long long ps = 0;
+    const PacDiv byL1 = pac_div_by(l1);
 #pragma unroll 4
     for (int i = 0; i < n; ++i) {
-        double xh = fabs(((double)K * vec[i * XS]) / l1);
+        double xh = fabs(pac_div((double)K * vec[i * XS], byL1));
         double p = floor(xh);
         res[i * XS] = xh - p;
         y[i * XS] = (int)p;
@@ -588,10 +589,11 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
                 const int n = nd.n, mid = n / 2, half = (n + 1) / 2, hc = nd.cap / 2;
                 double sm = 0.0, sd = 0.0;
                 const bool dv = nr != 0.0;
+                const PacDiv byNr = pac_div_by(dv ? nr : 1.0);
                 int i = 0;
                 for (; i + 2 <= mid; i += 2) {                 // two elements per trip: four loads in flight
                     double l0 = cur[i * XS], l1 = cur[(i + 1) * XS], r0 = cur[(mid + i) * XS], r1 = cur[(mid + i + 1) * XS];
-                    if (dv) { l0 = l0 / nr; l1 = l1 / nr; r0 = r0 / nr; r1 = r1 / nr; }
+                    if (dv) { l0 = pac_div(l0, byNr); l1 = pac_div(l1, byNr); r0 = pac_div(r0, byNr); r1 = pac_div(r1, byNr); }
                     const double M0 = (l0 + r0) / 2.0, S0 = (l0 - r0) / 2.0, M1 = (l1 + r1) / 2.0, S1 = (l1 - r1) / 2.0;
                     oth[i * XS] = M0; oth[(hc + i) * XS] = S0; oth[(i + 1) * XS] = M1; oth[(hc + i + 1) * XS] = S1;
                     sm += M0 * M0; sd += S0 * S0;
@@ -600,7 +602,7 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
                 for (; i < half; ++i) {
                     double l = i < mid ? cur[i * XS] : 0.0;           // odd n: the LEFT half is zero padded at its end
                     double r = cur[(mid + i) * XS];
-                    if (dv) { l = l / nr; r = r / nr; }
+                    if (dv) { l = pac_div(l, byNr); r = pac_div(r, byNr); }
                     const double M = (l + r) / 2.0, S = (l - r) / 2.0;
                     oth[i * XS] = M;
                     oth[(hc + i) * XS] = S;
@@ -635,12 +637,14 @@ __device__ __forceinline__ int thread_quantize_gain_shape(const PvqTab& t, const
                 // the leaf search reads its vector three times: normalise it once, in place (a root leaf: into wsA)
                 double* vec = (nd.buf ? wsB : wsA) + nd.off * XS;
                 if (nr != 0.0 && K != 0) {
+                    const PacDiv byNr = pac_div_by(nr);
                     int i = 0;
                     for (; i + 4 <= nd.n; i += 4) {
                         const double v0 = cur[i * XS], v1 = cur[(i + 1) * XS], v2 = cur[(i + 2) * XS], v3 = cur[(i + 3) * XS];
-                        vec[i * XS] = v0 / nr; vec[(i + 1) * XS] = v1 / nr; vec[(i + 2) * XS] = v2 / nr; vec[(i + 3) * XS] = v3 / nr;
+                        vec[i * XS] = pac_div(v0, byNr); vec[(i + 1) * XS] = pac_div(v1, byNr);
+                        vec[(i + 2) * XS] = pac_div(v2, byNr); vec[(i + 3) * XS] = pac_div(v3, byNr);
                     }
-                    for (; i < nd.n; ++i) vec[i * XS] = cur[i * XS] / nr;
+                    for (; i < nd.n; ++i) vec[i * XS] = pac_div(cur[i * XS], byNr);
                 }
                 const unsigned long long idx = thread_quantize_pvq<XS>(t, vec, oth, yws + nd.off * XS, nd.n, K, err);
                 tbw_put<XS>(out, idx, w);

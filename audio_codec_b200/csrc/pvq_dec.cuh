@@ -362,28 +362,31 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
                 } else {
                     pm_sincos_pair(nd.theta, &sn, &ct);
                 }
-                const double r2 = sqrt(2.0), nm = nd.nrMid, ns = nd.nrSide;
+                const double nm = nd.nrMid, ns = nd.nrSide;
                 const bool zm = nd.z & 1, zs = nd.z & 2;
+                // the three divisors of this node (pac_div: the IEEE quotient from one shared reciprocal each)
+                const PacDiv byNm = pac_div_by(nm != 0.0 ? nm : 1.0), byNs = pac_div_by(ns != 0.0 ? ns : 1.0);
+                const PacDiv byR2 = {__longlong_as_double(0x3FF6A09E667F3BCDLL), __longlong_as_double(0x3FE6A09E667F3BCCLL)};   // sqrt(2.0), RN(1 / sqrt(2.0))
                 double ss = 0.0;
                 int i = 0;
                 for (; i + 2 <= mid; i += 2) {                 // two elements per trip: up to four loads in flight
                     double m0 = 0.0, m1 = 0.0, s0 = 0.0, s1 = 0.0;
                     if (!zm) { m0 = oth[i * XS]; m1 = oth[(i + 1) * XS]; }
                     if (!zs) { s0 = oth[(hc + i) * XS]; s1 = oth[(hc + i + 1) * XS]; }
-                    if (nm != 0.0) { m0 = m0 / nm; m1 = m1 / nm; }
-                    if (ns != 0.0) { s0 = s0 / ns; s1 = s1 / ns; }
-                    const double l0 = (m0 * ct + s0 * sn) / r2, r0 = (m0 * ct - s0 * sn) / r2;
-                    const double l1 = (m1 * ct + s1 * sn) / r2, r1 = (m1 * ct - s1 * sn) / r2;
+                    if (nm != 0.0) { m0 = pac_div(m0, byNm); m1 = pac_div(m1, byNm); }
+                    if (ns != 0.0) { s0 = pac_div(s0, byNs); s1 = pac_div(s1, byNs); }
+                    const double l0 = pac_div(m0 * ct + s0 * sn, byR2), r0 = pac_div(m0 * ct - s0 * sn, byR2);
+                    const double l1 = pac_div(m1 * ct + s1 * sn, byR2), r1 = pac_div(m1 * ct - s1 * sn, byR2);
                     cur[i * XS] = l0; cur[(mid + i) * XS] = r0; cur[(i + 1) * XS] = l1; cur[(mid + i + 1) * XS] = r1;
                     ss += l0 * l0; ss += r0 * r0;
                     ss += l1 * l1; ss += r1 * r1;
                 }
                 for (; i < half; ++i) {
                     double m = zm ? 0.0 : oth[i * XS], s = zs ? 0.0 : oth[(hc + i) * XS];
-                    if (nm != 0.0) m = m / nm;
-                    if (ns != 0.0) s = s / ns;
-                    const double l = (m * ct + s * sn) / r2;
-                    const double r = (m * ct - s * sn) / r2;
+                    if (nm != 0.0) m = pac_div(m, byNm);
+                    if (ns != 0.0) s = pac_div(s, byNs);
+                    const double l = pac_div(m * ct + s * sn, byR2);
+                    const double r = pac_div(m * ct - s * sn, byR2);
                     if (i < mid) { cur[i * XS] = l; ss += l * l; }     // odd n: the padded last element of left is dropped
                     cur[(mid + i) * XS] = r;
                     ss += r * r;
@@ -410,14 +413,15 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
         for (int i = 0; i < L; ++i) out[i * XS] = gain;
     } else {
         int i = 0;
+        const PacDiv byRoot = pac_div_by(rootNr != 0.0 ? rootNr : 1.0);
         for (; i + 4 <= L; i += 4) {
             double v0 = shape[i * XS], v1 = shape[(i + 1) * XS], v2 = shape[(i + 2) * XS], v3 = shape[(i + 3) * XS];
-            if (rootNr != 0.0) { v0 = v0 / rootNr; v1 = v1 / rootNr; v2 = v2 / rootNr; v3 = v3 / rootNr; }
+            if (rootNr != 0.0) { v0 = pac_div(v0, byRoot); v1 = pac_div(v1, byRoot); v2 = pac_div(v2, byRoot); v3 = pac_div(v3, byRoot); }
             out[i * XS] = gain * v0; out[(i + 1) * XS] = gain * v1; out[(i + 2) * XS] = gain * v2; out[(i + 3) * XS] = gain * v3;
         }
         for (; i < L; ++i) {
             double v = shape[i * XS];
-            if (rootNr != 0.0) v = v / rootNr;
+            if (rootNr != 0.0) v = pac_div(v, byRoot);
             out[i * XS] = gain * v;
         }
     }

@@ -516,6 +516,10 @@ def main():
     nbs = [nb] * S
     hdr = [n] * S
     ctx = _lib.Context(sample_rate=FS, n_channels=2, rate_kbps=RATE, device=local)
+    if os.environ.get("PAC_BENCH_BATCH_CB"):                     # channel-blocks per launch of the thread-per-band kernels
+        ctx.set_option("batch_cb", int(os.environ["PAC_BENCH_BATCH_CB"]))
+    if os.environ.get("PAC_BENCH_HOST_CHUNK_MB"):                # smallest chunk of the host-buffer pipeline (MB of PCM)
+        ctx.set_option("host_chunk_mb", float(os.environ["PAC_BENCH_HOST_CHUNK_MB"]))
     if os.environ.get("PAC_BENCH_VARIANT"):                      # A/B timing of earlier kernel forms (same results)
         ctx.set_option("variant", int(os.environ["PAC_BENCH_VARIANT"]))
     cap = _lib.lib.pac_encode_bound(ctx.h, (__import__("ctypes").c_int * S)(*nbs), S)

@@ -184,6 +184,12 @@ int pac_psy_map(pac_ctx* ctx, int op, const double* d_x, long long n, double* d_
  * (-32768 -> 0.0), elementwise, as the stream encoder applies it. */
 int pac_pcm_to_float(pac_ctx* ctx, const short* d_pcm, long long n, double* d_out, void* stream);
 
+/* Self-test (no reference counterpart): the quantiser kernels form x / d for many x and one d (a vector norm,
+ * sqrt(2)) from one correctly rounded reciprocal and a residual correction (pac_div, csrc/pac_common.cuh), which
+ * equals the IEEE quotient.  Runs n_pairs pseudo-random pairs on the device and returns how many quotients differ
+ * from the division instruction (expected 0), or a negative pac_status. */
+long long pac_selftest_division(pac_ctx* ctx, long long n_pairs, unsigned long long seed, void* stream);
+
 /* bitalloc.BitAlloc(bitBudget, maxMantBits, nBands, nLines, SMR) (coder/bitalloc.py:62-121);
  * BitAlloc_SBR is the same call with nLines[omitted] = 1 (coder/bitalloc.py:123-145). */
 int pac_bit_alloc(pac_ctx* ctx, const double* d_budget, int max_mant_bits, int n_bands, const int* h_nlines,

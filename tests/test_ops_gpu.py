@@ -368,3 +368,14 @@ def test_straight_line_transcendentals_are_bit_identical_to_the_library_calls():
             _lib.check(_lib.lib.pac_psy_map(ctx.h, op, C.c_void_p(d.data_ptr()), d.numel(), C.c_void_p(o.data_ptr()),
                                             _lib.stream_ptr()))
         assert torch.equal(o1.view(torch.int64), o2.view(torch.int64)), int((o1 != o2).sum())
+
+
+def test_shared_reciprocal_division_equals_ieee_division():
+    """pac_div (one correctly rounded reciprocal per divisor + residual correction, csrc/pac_common.cuh) is what
+    the thread-per-band quantisers use for x / norm and x / sqrt(2): it must be the IEEE quotient bit for bit
+    (Markstein).  2^27 pseudo-random pairs in four magnitude classes, two seeds."""
+    from audio_codec_b200 import _lib
+    ctx = _lib.default_context(48000)
+    for seed in (1, 0xC0FFEE):
+        bad = _lib.lib.pac_selftest_division(ctx.h, 1 << 26, seed, _lib.stream_ptr())
+        assert bad == 0, f"{bad} quotients differ from the division instruction"
