@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <vector>
 #include "decode_frame.cuh"
+#include "decode_long.cuh"
 #include "pac_api.h"
 
 extern "C" int pac_header_bytes(const pac_ctx* ctx);
@@ -237,20 +238,37 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
 #ifndef DEC_PRE_MINB
 #define DEC_PRE_MINB 4
 #endif
+#define DEC_PRE_RANGE 64      // channel-blocks a CTA of k_decode<T, true> looks at (it decodes the ones k_decode_long leaves)
 template <typename T, bool PRE>
 __global__ void __launch_bounds__(DEC_NT, PRE ? DEC_PRE_MINB : 3)
-k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines) {
+k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines,
+         int nCb, int split) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int s_list[DEC_PRE_RANGE];
+    __shared__ int s_n;
     DecSmem S;
     dec_smem_carve(smem_raw, S, PRE);
     const int tid = threadIdx.x;
-    const long long cb = (long long)blockIdx.x + a.cb0;
+    int nMine = 1;
+    if (PRE && split) {
+        // behind k_decode_long: this CTA owns DEC_PRE_RANGE consecutive channel-blocks and decodes the transient and
+        // SBR ones among them (a few per cent of a stream)
+        if (tid == 0) s_n = 0;
+        __syncthreads();
+        const int i = blockIdx.x * DEC_PRE_RANGE + tid;
+        if (tid < DEC_PRE_RANGE && i < nCb && !dl_takes(preAll[i].flags, preAll[i].sbr)) s_list[atomicAdd(&s_n, 1)] = i;
+        __syncthreads();
+        nMine = s_n;
+    }
+    for (int j = 0; j < nMine; ++j) {
+    const int local = (PRE && split) ? s_list[j] : (int)blockIdx.x;
+    const long long cb = (long long)local + a.cb0;
     int nBytes = a.payBytes[cb];
     if (nBytes > DEC_REC_MAX) {
         if (tid == 0) atomicOr(a.err, PVQ_ERR_STACK);
         nBytes = DEC_REC_MAX;
     }
-    const CbHdr* pre = PRE ? preAll + blockIdx.x : nullptr;
+    const CbHdr* pre = PRE ? preAll + local : nullptr;
     const unsigned char* src = a.buf + a.payOff[cb];
     if (!pre) for (int i = tid; i < nBytes; i += DEC_NT) S.rec[i] = src[i];
     for (int i = tid; i < 2048; i += DEC_NT) S.y[i] = 0.0;
@@ -263,14 +281,16 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ pr
     if (nBytes > 0) {
         if (!cur) {
             int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err, pre, preLines, blockIdx.x, 0);
+            decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err, pre, preLines, local, 0);
         } else {
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err, pre, preLines, blockIdx.x, sf);
+                decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err, pre, preLines, local, sf);
         }
     }
     double* dst = a.frames + cb * 2048;
     for (int i = tid; i < 2048; i += DEC_NT) dst[i] = S.y[i];
+    __syncthreads();
+    }
 }
 
 // PCM quantiser of the WAV writer (coder/pcmfile.py:127-134): sign-magnitude midtread, 16 bit.
@@ -420,6 +440,8 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
         PAC_CHECK(cudaFuncSetAttribute(k_decode<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PAC_CHECK(cudaFuncSetAttribute(k_decode<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemL));
         PAC_CHECK(cudaFuncSetAttribute(k_decode<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemL));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode_long<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dl_smem_bytes<double>()));
+        PAC_CHECK(cudaFuncSetAttribute(k_decode_long<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dl_smem_bytes<float>()));
         if (c == 0) cudaEventRecord(ctx->ev[2], st);      // pac_last_kernel_ms: the first chunk (the only one unless chunked)
         for (long long q0 = 0; q0 < nCbC; q0 += vq ? batchCb : nCbC) {
             const long long nq = vq ? std::min(batchCb, nCbC - q0) : nCbC;
@@ -439,12 +461,25 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
                 ++ctx->launches;      // k_hdr
             }
             pac_kev_begin(ctx, 3, st);
-            if (vq) {
-                if (ctx->cfg.precision == PAC_F32) k_decode<float, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines);
-                else k_decode<double, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines);
+            if (vq && !(ctx->optVariant & 16)) {
+                // long blocks: one warp each (decode_long.cuh); transient and SBR blocks: the CTA-per-block kernel
+                const unsigned gL = (unsigned)std::min<long long>(148, (nq + DL_WARPS - 1) / DL_WARPS);
+                const unsigned gS = (unsigned)((nq + DEC_PRE_RANGE - 1) / DEC_PRE_RANGE);
+                double* fr = a.frames + a.cb0 * 2048;
+                if (ctx->cfg.precision == PAC_F32) {
+                    k_decode_long<float><<<gL, DL_WARPS * 32, dl_smem_bytes<float>(), st>>>(ctx->dev, fr, (int)nq, dPre, dLines);
+                    k_decode<float, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 1);
+                } else {
+                    k_decode_long<double><<<gL, DL_WARPS * 32, dl_smem_bytes<double>(), st>>>(ctx->dev, fr, (int)nq, dPre, dLines);
+                    k_decode<double, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 1);
+                }
+                ++ctx->launches;
+            } else if (vq) {
+                if (ctx->cfg.precision == PAC_F32) k_decode<float, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
+                else k_decode<double, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
             } else {
-                if (ctx->cfg.precision == PAC_F32) k_decode<float, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
-                else k_decode<double, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines);
+                if (ctx->cfg.precision == PAC_F32) k_decode<float, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
+                else k_decode<double, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
             }
             pac_kev_end(ctx, 3, st);
         }

@@ -336,8 +336,9 @@ __device__ __forceinline__ void thread_dequantize_gain_shape(const PvqTab& t, Bi
                 double nrOut = sqrt(pvq_vector<XS>(t, idx, nd.n, K, cur, err));
                 if (nd.root) {                            // a root leaf is normalised twice (:214-218)
                     double ss = 0.0;
+                    const PacDiv byNr = pac_div_by(nrOut != 0.0 ? nrOut : 1.0);
                     for (int i = 0; i < nd.n; ++i) {
-                        const double c = nrOut != 0.0 ? cur[i * XS] / nrOut : cur[i * XS];
+                        const double c = nrOut != 0.0 ? pac_div(cur[i * XS], byNr) : cur[i * XS];
                         cur[i * XS] = c;
                         ss += c * c;
                     }
