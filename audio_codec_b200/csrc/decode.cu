@@ -164,6 +164,8 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
     if (fl & 0x80u) p = ((fl >> 1) & 1) ? nCb - 1 - atomicAdd(&counts[1], 1) : atomicAdd(&counts[0], 1);
     h->p = p;
     if (p >= 0) perm[p] = local;
+    // transient and SBR blocks stay with the CTA-per-block kernel: a work list it pulls from (counts[2] entries)
+    if (!dl_takes(fl, sbrF)) (counts + 4)[atomicAdd(&counts[2], 1)] = local;
 }
 
 // k_dequant: one thread per (channel-block, band).  A CTA holds one band slot of DQ_NT consecutive
@@ -238,30 +240,28 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
 #ifndef DEC_PRE_MINB
 #define DEC_PRE_MINB 4
 #endif
-#define DEC_PRE_RANGE 64      // channel-blocks a CTA of k_decode<T, true> looks at (it decodes the ones k_decode_long leaves)
 template <typename T, bool PRE>
 __global__ void __launch_bounds__(DEC_NT, PRE ? DEC_PRE_MINB : 3)
 k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines,
-         int nCb, int split) {
+         int* __restrict__ work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ int s_list[DEC_PRE_RANGE];
-    __shared__ int s_n;
+    __shared__ int s_next;
     DecSmem S;
     dec_smem_carve(smem_raw, S, PRE);
     const int tid = threadIdx.x;
-    int nMine = 1;
-    if (PRE && split) {
-        // behind k_decode_long: this CTA owns DEC_PRE_RANGE consecutive channel-blocks and decodes the transient and
-        // SBR ones among them (a few per cent of a stream)
-        if (tid == 0) s_n = 0;
+    // work (behind k_decode_long): counts[2] = number of listed blocks, counts[3] = next to hand out, list at
+    // counts + 4.  A fixed grid of CTAs pulls blocks until the list is empty (transient blocks come in bursts: a
+    // static split leaves most CTAs idle).  Without a list: one CTA per channel-block.
+    for (;;) {
+    int local = (int)blockIdx.x;
+    if (PRE && work) {
+        if (tid == 0) s_next = atomicAdd(&work[3], 1);
         __syncthreads();
-        const int i = blockIdx.x * DEC_PRE_RANGE + tid;
-        if (tid < DEC_PRE_RANGE && i < nCb && !dl_takes(preAll[i].flags, preAll[i].sbr)) s_list[atomicAdd(&s_n, 1)] = i;
+        const int j = s_next;
         __syncthreads();
-        nMine = s_n;
+        if (j >= work[2]) break;
+        local = (work + 4)[j];
     }
-    for (int j = 0; j < nMine; ++j) {
-    const int local = (PRE && split) ? s_list[j] : (int)blockIdx.x;
     const long long cb = (long long)local + a.cb0;
     int nBytes = a.payBytes[cb];
     if (nBytes > DEC_REC_MAX) {
@@ -289,6 +289,7 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ pr
     }
     double* dst = a.frames + cb * 2048;
     for (int i = tid; i < 2048; i += DEC_NT) dst[i] = S.y[i];
+    if (!(PRE && work)) break;
     __syncthreads();
     }
 }
@@ -410,7 +411,7 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     size_t oPre = carve((size_t)batchCb * sizeof(CbHdr));
     size_t oLines = carve((size_t)batchGroups * 32 * 1024 * sizeof(double));
     size_t oWs = carve((size_t)batchGroups * 32 * 2 * PRE_WS_PER_CB * sizeof(double));
-    size_t oPerm = carve((size_t)(batchCb + 2) * sizeof(int));
+    size_t oPerm = carve((size_t)(2 * batchCb + 4) * sizeof(int));     // perm | counts[4] | blocks left to k_decode
     void* scr = nullptr;
     if ((rc = pac_scratch(ctx, o, &scr))) return rc;
     unsigned char* sb = (unsigned char*)scr;
@@ -448,11 +449,11 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
             a.cb0 = cb0 + q0;
             CbHdr* dPre = vq ? (CbHdr*)(sb + oPre) : nullptr;
             double* dLines = vq ? (double*)(sb + oLines) : nullptr;
+            int* dPerm = (int*)(sb + oPerm);
+            int* dCounts = dPerm + batchCb;
             if (vq) {
                 const int nChunks = (int)((nq + DQ_NT - 1) / DQ_NT);
-                int* dPerm = (int*)(sb + oPerm);
-                int* dCounts = dPerm + batchCb;
-                PAC_CHECK(cudaMemsetAsync(dCounts, 0, 2 * sizeof(int), st));
+                PAC_CHECK(cudaMemsetAsync(dCounts, 0, 4 * sizeof(int), st));
                 k_hdr<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, dPre, dPerm, dCounts);
                 pac_kev_begin(ctx, 2, st);
                 k_dequant<<<(unsigned)(nChunks * PRE_SLOTS), DQ_NT, 0, st>>>(ctx->dev, a, a.cb0, (int)nq, nChunks, dPre, dLines,
@@ -464,22 +465,22 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
             if (vq && !(ctx->optVariant & 16)) {
                 // long blocks: one warp each (decode_long.cuh); transient and SBR blocks: the CTA-per-block kernel
                 const unsigned gL = (unsigned)std::min<long long>(148, (nq + DL_WARPS - 1) / DL_WARPS);
-                const unsigned gS = (unsigned)((nq + DEC_PRE_RANGE - 1) / DEC_PRE_RANGE);
+                const unsigned gS = (unsigned)std::min<long long>(148 * DEC_PRE_MINB, nq);
                 double* fr = a.frames + a.cb0 * 2048;
                 if (ctx->cfg.precision == PAC_F32) {
                     k_decode_long<float><<<gL, DL_WARPS * 32, dl_smem_bytes<float>(), st>>>(ctx->dev, fr, (int)nq, dPre, dLines);
-                    k_decode<float, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 1);
+                    k_decode<float, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, dCounts);
                 } else {
                     k_decode_long<double><<<gL, DL_WARPS * 32, dl_smem_bytes<double>(), st>>>(ctx->dev, fr, (int)nq, dPre, dLines);
-                    k_decode<double, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 1);
+                    k_decode<double, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, dCounts);
                 }
                 ++ctx->launches;
             } else if (vq) {
-                if (ctx->cfg.precision == PAC_F32) k_decode<float, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
-                else k_decode<double, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
+                if (ctx->cfg.precision == PAC_F32) k_decode<float, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, nullptr);
+                else k_decode<double, true><<<(unsigned)nq, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, nullptr);
             } else {
-                if (ctx->cfg.precision == PAC_F32) k_decode<float, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
-                else k_decode<double, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines, (int)nq, 0);
+                if (ctx->cfg.precision == PAC_F32) k_decode<float, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines, nullptr);
+                else k_decode<double, false><<<(unsigned)nq, DEC_NT, smem, st>>>(ctx->dev, a, dPre, dLines, nullptr);
             }
             pac_kev_end(ctx, 3, st);
         }
