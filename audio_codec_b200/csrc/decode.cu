@@ -468,10 +468,10 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
                 const unsigned gS = (unsigned)std::min<long long>(148 * DEC_PRE_MINB, nq);
                 double* fr = a.frames + a.cb0 * 2048;
                 if (ctx->cfg.precision == PAC_F32) {
-                    k_decode_long<float><<<gL, DL_WARPS * 32, dl_smem_bytes<float>(), st>>>(ctx->dev, fr, (int)nq, dPre, dLines);
+                    k_decode_long<float><<<gL, DL_WARPS * 32, dl_smem_bytes<float>(), st>>>(ctx->dev, fr, dPre, dLines, dPerm, dCounts);
                     k_decode<float, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, dCounts);
                 } else {
-                    k_decode_long<double><<<gL, DL_WARPS * 32, dl_smem_bytes<double>(), st>>>(ctx->dev, fr, (int)nq, dPre, dLines);
+                    k_decode_long<double><<<gL, DL_WARPS * 32, dl_smem_bytes<double>(), st>>>(ctx->dev, fr, dPre, dLines, dPerm, dCounts);
                     k_decode<double, true><<<gS, DEC_NT, smemL, st>>>(ctx->dev, a, dPre, dLines, dCounts);
                 }
                 ++ctx->launches;

@@ -5,14 +5,14 @@
 // barrier per stage: 27 k cycles per block, 8.4 ms per step, although the work is the streaming IMDCT's
 // (mdct_stream.cuh: 1.5 ms for the same number of frames).  Here a channel-block belongs to ONE WARP:
 //   * the warp gathers the block's column of the lane-interleaved line array k_dequant wrote (8 bytes out of every
-//     256-byte row; the four blocks that share a 32-byte sector are neighbours in the batch and are read by
-//     neighbouring warps, so HBM sees each sector once), scales and pre-twiddles in registers;
+//     256-byte row; the kernel walks the batch in its dense order, so the 32 blocks of a row are read by
+//     neighbouring warps in the same pass and HBM sees each row once), scales and pre-twiddles in registers;
 //   * warp_fft512 (16 x 16 x 2 in registers, one skewed shared-memory exchange, __syncwarp only);
 //   * post-twiddle into the warp's staging tile, then the unfolded samples times the window of the block's shape
 //     (read through L1 from the 5-shape table: almost every block uses the sine shape) leave as 16-byte stores.
 // No CTA barrier after the tables are loaded; 16 warps per SM in both precisions.
 // Blocks the kernel does not take - transient blocks (8 short frames) and long blocks with SBR reconstruction - are
-// left to k_decode<T, true>, which skips the ones handled here; a block without a record is zero filled here.
+// left to k_decode<T, true> (k_hdr lists them), as is the zero fill of a block without a record.
 #pragma once
 #include "mdct_stream.cuh"
 #include "decode_frame.cuh"
@@ -23,17 +23,15 @@ template <typename T> __host__ __device__ constexpr size_t dl_smem_bytes() {
     // twiddles + second-pass roots + roots (1024 complex) + per warp the exchange / staging tile
     return sizeof(T) * (2 * 1024 + (size_t)DL_WARPS * 2 * MS_TILE);
 }
-
 // true: k_decode_long writes this block's frame; false: k_decode<T, true> does
 __device__ __forceinline__ bool dl_takes(unsigned char flags, unsigned char sbr) {
-    if (!(flags & 0x80u)) return true;                    // no record: zeros
-    return !((flags >> 1) & 1) && !sbr;                   // long, no SBR reconstruction
+    return (flags & 0x80u) && !((flags >> 1) & 1) && !sbr;     // a record, long, no SBR reconstruction
 }
 
 template <typename T>
 __global__ void __launch_bounds__(DL_WARPS * 32, 1)
-k_decode_long(const PacDev* __restrict__ dev, double* __restrict__ frames, int nCb, const CbHdr* __restrict__ hdrs,
-              const double* __restrict__ lines) {
+k_decode_long(const PacDev* __restrict__ dev, double* __restrict__ frames, const CbHdr* __restrict__ hdrs,
+              const double* __restrict__ lines, const int* __restrict__ perm, const int* __restrict__ counts) {
     constexpr int M = 1024, Q = 512, W = DL_WARPS;
     constexpr int NV = MsBlock<T>::NV, PER = MsBlock<T>::PER, L = MsRun<T>::L;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -54,22 +52,23 @@ k_decode_long(const PacDev* __restrict__ dev, double* __restrict__ frames, int n
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const T* winAll = t.win_long;
     T* Ev = reinterpret_cast<T*>(tb.roots + 256) + (size_t)warp * 2 * MS_TILE;     // DCT-IV output, even indices (skewed)
     T* Ov = Ev + MS_TILE;                                                            // odd indices
-    const T* winAll = t.win_long;
-    for (int cb = blockIdx.x * W + warp; cb < nCb; cb += gridDim.x * W) {
+    // in the batch's DENSE order (k_hdr: long blocks from the front): the 32 blocks of a 256-byte row of the line array
+    // are then read by 32 neighbouring warps in the same pass, whatever the blocks' places in the streams (in stream
+    // order a row's blocks can be far apart once transient blocks have shifted the dense order, and HBM delivered
+    // 2.4 x the algorithmic bytes)
+    const int nLong = counts[0];
+    for (int p = blockIdx.x * W + warp; p < nLong; p += gridDim.x * W) {
+        const int cb = perm[p];
         const CbHdr* h = hdrs + cb;
         const unsigned char fl = h->flags;
         if (!dl_takes(fl, h->sbr)) continue;
         double* dst = frames + (size_t)cb * 2048;
-        if (!(fl & 0x80u)) {
-            for (int i = lane; i < 1024; i += 32) reinterpret_cast<double2*>(dst)[i] = make_double2(0.0, 0.0);
-            continue;
-        }
         const bool last = (fl >> 2) & 1, nxt = fl & 1;
         const int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
         const double inv = 1.0 / (double)(1 << h->scale[0]);
-        const int p = h->p;
         const double* src = lines + ((size_t)(p >> 5) * 1024) * 32 + (size_t)(p & 31);
         cplx<T> u[16];
 #pragma unroll
