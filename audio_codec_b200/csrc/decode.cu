@@ -322,9 +322,16 @@ __global__ void k_ola(const double* __restrict__ frames, const long long* __rest
     const double* head = b < nBlk ? frames + (cbOff[s] + b * C + c) * 2048 : nullptr;
     const double* tail = b > 0 ? frames + (cbOff[s] + (b - 1) * C + c) * 2048 + 1024 : nullptr;
     short* dst = pcm + pcmOff[s] + ((long long)c * (nBlk + 1) + b) * 1024;
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
-        double v = (tail ? tail[i] : 0.0) + (head ? head[i] : 0.0);
-        dst[i] = double_to_pcm(v);
+    // four samples per thread: 2 x 32 bytes in, 8 bytes out (the caller's buffer may be 2-byte aligned only)
+    const bool vec = ((unsigned long long)dst & 7ull) == 0ull;
+    for (int i = threadIdx.x * 4; i < 1024; i += blockDim.x * 4) {
+        double2 t0 = make_double2(0.0, 0.0), t1 = t0, h0 = t0, h1 = t0;
+        if (tail) { t0 = *reinterpret_cast<const double2*>(tail + i); t1 = *reinterpret_cast<const double2*>(tail + i + 2); }
+        if (head) { h0 = *reinterpret_cast<const double2*>(head + i); h1 = *reinterpret_cast<const double2*>(head + i + 2); }
+        const short q0 = double_to_pcm(t0.x + h0.x), q1 = double_to_pcm(t0.y + h0.y);
+        const short q2 = double_to_pcm(t1.x + h1.x), q3 = double_to_pcm(t1.y + h1.y);
+        if (vec) *reinterpret_cast<short4*>(dst + i) = make_short4(q0, q1, q2, q3);
+        else { dst[i] = q0; dst[i + 1] = q1; dst[i + 2] = q2; dst[i + 3] = q3; }
     }
 }
 

@@ -12,6 +12,8 @@
 #include "encode_frame.cuh"
 
 #define ENF_NT 128
+#define ENF_SHORT_MAXM 72          // masker capacity of a short frame (at most 65 peaks in 129 bins)
+#define ENF_SHORT_DOUBLES 760      // per-warp buffers of the short-frame path (see k_encode_front); 4 x 760 <= 2048 + 1024 + 1026
 #ifndef ENF_MINB
 #define ENF_MINB 6
 #endif
@@ -88,11 +90,15 @@ __device__ __forceinline__ void enf_fold(const short* x, const T* __restrict__ w
 }
 
 // One frame of N samples (int16 codes at x): steps (1)-(3) of encode_frame() and the hand-off of encode_back().
+// NT = ENF_NT: the CTA works on one frame.  NT = 32: every WARP of the CTA works on a frame of its own (S: the warp's
+// buffers) - the eight short frames of a transient block, four at a time; the barriers stay CTA-wide (every warp
+// passes the same unconditional barriers), so the four frames advance in step.  cand: band_smr_pruned's candidate
+// list ([N / 2] ints; may be null when NT >= N / 2).
 template <int N, typename T, int NT>
 __device__ __forceinline__ void enf_frame(const PacDev* __restrict__ dev, const EnfSmem& S, const short* x, int shape,
-                                          bool sbr, EncPre* hdr, double* linesOut, int sf) {
+                                          bool sbr, EncPre* hdr, double* linesOut, int sf, int* cand) {
     constexpr int H = N / 2, Q = N / 4;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = NT == 32 ? (int)(threadIdx.x & 31) : (int)threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const PacBands& bands = (N == PAC_NLONG) ? dev->longBands : dev->shortBands;
     const int nB = bands.nBands;
     const PsyConst<T> pc = psy_const<N, T>(dev);
@@ -152,10 +158,9 @@ __device__ __forceinline__ void enf_frame(const PacDev* __restrict__ dev, const 
     ENF_PH(5);
 
     // (3) psychoacoustic model -> SMR per band
-    const MaskerList<T> ml = masker_list<T>(reinterpret_cast<T*>(S.fb));
+    const MaskerList<T> ml = masker_list<T, (N == PAC_NLONG ? PSY_MAX_MASKERS : ENF_SHORT_MAXM)>(reinterpret_cast<T*>(S.fb));
     const int nMask = pick_maskers<N, NT, T, true>(mkT, pc, ml, tid);
-    band_smr_pruned<N, NT, T>(pc, ml, nMask, S.lines, scale, mkT, bands, S.smr, S.tmp,
-                              N == PAC_NLONG ? reinterpret_cast<int*>(S.xs) : nullptr, tid);
+    band_smr_pruned<N, NT, T>(pc, ml, nMask, S.lines, scale, mkT, bands, S.smr, S.tmp, cand, tid);
 
     // hand-off to k_bitalloc / k_pvq / k_pack
     for (int i = tid; i < H; i += NT) linesOut[(size_t)(sf * PAC_HALF_SHORT + i) * 32] = S.lines[i];
@@ -220,7 +225,8 @@ k_encode_front(const PacDev* __restrict__ dev, EncArgs a) {
     double* linesOut = a.preLines + epre_line_index(S.misc[8], 0);
     if (!cur) {
         const int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
-        enf_frame<PAC_NLONG, T, ENF_NT>(dev, S, S.xs, shape, dev->useSBR != 0, hdr, linesOut, 0);
+        enf_frame<PAC_NLONG, T, ENF_NT>(dev, S, S.xs, shape, dev->useSBR != 0, hdr, linesOut, 0,
+                                        reinterpret_cast<int*>(S.xs));        // the frame is dead by then
     } else {
         // zero sub-frame check (coder/pacfile.py:503-506): the block is dropped if ANY channel has one.
         // A code maps to 0.0 iff its magnitude bits are zero (0 and -32768, coder/pcmfile.py:89-98).
@@ -229,8 +235,21 @@ k_encode_front(const PacDev* __restrict__ dev, EncArgs a) {
             for (int i = tid; i < PAC_NSHORT; i += ENF_NT) nz |= (S.xs[448 + 128 * sf + i] & 0x7fff) != 0;
             if (!__syncthreads_or(nz) && tid == 0) S.misc[4] = 1;
         }
-        for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
-            enf_frame<PAC_NSHORT, T, ENF_NT>(dev, S, S.xs + 448 + 128 * sf, PAC_WIN_SINE, false, hdr, linesOut, sf);
+        // the eight short frames: one per warp, four at a time (a short frame keeps 32 lanes busy, not 128, and a
+        // transient block cost six long ones when its frames ran one after the other on the whole CTA)
+        static_assert(ENF_NT == 128 && PAC_SUBFRAMES == 8, "two rounds of four short frames");
+        EnfSmem W = S;
+        double* wb0 = S.fb + (size_t)(tid >> 5) * ENF_SHORT_DOUBLES;
+        W.fb = wb0;             // [352] FFT buffers, then the masker list
+        W.lines = wb0 + 352;    // [128]
+        W.mk = wb0 + 480;       // [136]
+        W.smr = wb0 + 616;      // [32]
+        W.tmp = wb0 + 648;      // [48]
+        int* candW = reinterpret_cast<int*>(wb0 + 696);      // [128]
+        for (int r = 0; r < 2; ++r) {
+            const int sf = 4 * r + (tid >> 5);
+            enf_frame<PAC_NSHORT, T, 32>(dev, W, S.xs + 448 + 128 * sf, PAC_WIN_SINE, false, hdr, linesOut, sf, candW);
+        }
     }
     __syncthreads();
     if (tid == 0) {

@@ -40,13 +40,33 @@ __device__ __forceinline__ double pvq_vector(const PvqTab& t, unsigned long long
         }
         const unsigned long long nlk = pvq_N(t, l, k);
         long long lo = 1, hi = k;
-        while (lo < hi) {
-            long long mid = (lo + hi + 1) >> 1;
-            unsigned long long a = nlk - pvq_N(t, l, k - mid) - pvq_N(t, l - 1, k - mid);
-            if (a <= r) lo = mid; else hi = mid - 1;
+        unsigned long long nj, nlj;                       // N(l-1, k-lo), N(l, k-lo)
+        if (l >= 5) {
+            // both rows come from the table: fetch their bases once instead of once per probe (same values as pvq_N)
+            const int oL = t.off[l], o1 = t.off[l - 1];
+            const int lenL = t.off[l + 1] - oL, len1 = oL - o1;
+            const unsigned long long* rowL = t.N + oL;
+            const unsigned long long* row1 = t.N + o1;
+            const unsigned long long big = 1ull << 40;
+            while (lo < hi) {
+                const long long mid = (lo + hi + 1) >> 1, x = k - mid;        // 0 <= x < k
+                const unsigned long long vL = x == 0 ? 1ull : (x >= lenL ? big : rowL[x]);
+                const unsigned long long v1 = x == 0 ? 1ull : (x >= len1 ? big : row1[x]);
+                if (nlk - vL - v1 <= r) lo = mid; else hi = mid - 1;
+            }
+            const long long x = k - lo;
+            nlj = x == 0 ? 1ull : (x >= lenL ? big : rowL[x]);
+            nj = x == 0 ? 1ull : (x >= len1 ? big : row1[x]);
+        } else {
+            while (lo < hi) {
+                long long mid = (lo + hi + 1) >> 1;
+                unsigned long long a = nlk - pvq_N(t, l, k - mid) - pvq_N(t, l - 1, k - mid);
+                if (a <= r) lo = mid; else hi = mid - 1;
+            }
+            nj = pvq_N(t, l - 1, k - lo);
+            nlj = pvq_N(t, l, k - lo);
         }
-        const unsigned long long nj = pvq_N(t, l - 1, k - lo);
-        r -= nlk - pvq_N(t, l, k - lo) - nj;
+        r -= nlk - nlj - nj;
         bool neg = false;
         if (r >= nj) { neg = true; r -= nj; }
         if (r >= nj) { *err |= PVQ_ERR_DEGENERATE; r = 0ull; }    // index outside the codebook
