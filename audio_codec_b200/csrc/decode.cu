@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(WALK_WARPS * 32)
 k_walk(const unsigned char* __restrict__ buf, const long long* __restrict__ streamOff, int nStreams,
        int headerBytes, int* __restrict__ counts, const long long* __restrict__ cbOff,
        long long* __restrict__ payOff, int* __restrict__ payBytes) {
-    __shared__ __align__(16) unsigned char win[WALK_WARPS][WALK_WIN];
+    __shared__ __align__(16) unsigned char win[WALK_WARPS][WALK_WIN + 16];
     __shared__ long long s_pos[WALK_WARPS];
     __shared__ int s_n[WALK_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -43,33 +43,49 @@ k_walk(const unsigned char* __restrict__ buf, const long long* __restrict__ stre
     while (!done && pos + 4 <= end) {
         // window of 16-byte chunks (absolute alignment) starting at the chunk that holds pos
         const long long w0 = (long long)(((addr0 + (unsigned long long)pos) & ~15ull) - addr0);
+        if (w0 >= 0 && w0 + WALK_WIN <= bufEnd) {          // interior window: no per-chunk bounds checks
+            const uint4* src = reinterpret_cast<const uint4*>(buf + w0) + lane;
+            uint4 v[WALK_WIN / 512];
 #pragma unroll
-        for (int j = 0; j < WALK_WIN / 512; ++j) {
-            const long long o = w0 + (j * 32 + lane) * 16;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (o >= 0 && o + 16 <= bufEnd) v = __ldg(reinterpret_cast<const uint4*>(buf + o));
-            else if (o + 16 > 0 && o < bufEnd) {           // first / last partial chunk of the buffer: byte loads, nothing outside [0, bufEnd)
-                __align__(16) unsigned char t[16];
+            for (int j = 0; j < WALK_WIN / 512; ++j) v[j] = __ldg(src + j * 32);
 #pragma unroll
-                for (int b = 0; b < 16; ++b) t[b] = (o + b >= 0 && o + b < bufEnd) ? buf[o + b] : (unsigned char)0;
-                v = *reinterpret_cast<uint4*>(t);
+            for (int j = 0; j < WALK_WIN / 512; ++j) *reinterpret_cast<uint4*>(&win[warp][(j * 32 + lane) * 16]) = v[j];
+        } else {
+#pragma unroll 1
+            for (int j = 0; j < WALK_WIN / 512; ++j) {
+                const long long o = w0 + (j * 32 + lane) * 16;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (o >= 0 && o + 16 <= bufEnd) v = __ldg(reinterpret_cast<const uint4*>(buf + o));
+                else if (o + 16 > 0 && o < bufEnd) {       // first / last partial chunk of the buffer: byte loads, nothing outside [0, bufEnd)
+                    __align__(16) unsigned char t[16];
+#pragma unroll
+                    for (int b = 0; b < 16; ++b) t[b] = (o + b >= 0 && o + b < bufEnd) ? buf[o + b] : (unsigned char)0;
+                    v = *reinterpret_cast<uint4*>(t);
+                }
+                *reinterpret_cast<uint4*>(&win[warp][(j * 32 + lane) * 16]) = v;
             }
-            *reinterpret_cast<uint4*>(&win[warp][(j * 32 + lane) * 16]) = v;
         }
         __syncwarp();
         if (lane == 0) {
-            const long long wEnd = w0 + WALK_WIN;
-            while (pos + 4 <= end && pos + 4 <= wEnd) {
-                const unsigned char* q = &win[warp][pos - w0];
-                const unsigned nb = (unsigned)q[0] | ((unsigned)q[1] << 8) | ((unsigned)q[2] << 16) | ((unsigned)q[3] << 24);
-                if (pos + 4 + (long long)nb > end) { done = true; break; }      // truncated block
+            // the chain inside the window, window-relative; a prefix at any byte alignment is two aligned words and a
+            // funnel shift (the row is padded so that the second word always exists)
+            const unsigned* w32 = reinterpret_cast<const unsigned*>(&win[warp][0]);
+            const long long endRel = end - w0, lim = endRel < WALK_WIN ? endRel : (long long)WALK_WIN;
+            long long p = pos - w0;
+            while (p + 4 <= lim) {
+                const int pi = (int)p;
+                const unsigned lo = w32[pi >> 2], hi = w32[(pi >> 2) + 1];
+                const unsigned nb = __funnelshift_r(lo, hi, (pi & 3) * 8);
+                const long long np = p + 4 + (long long)nb;
+                if (np > endRel) { done = true; break; }   // truncated block
                 if (payOff && n < limit) {                 // a damaged stream may end on a partial block: its
-                    payOff[base + n] = pos + 4;             // extra record must not land in the next stream's slot
+                    payOff[base + n] = w0 + p + 4;          // extra record must not land in the next stream's slot
                     payBytes[base + n] = (int)nb;
                 }
                 ++n;
-                pos += 4 + nb;
+                p = np;
             }
+            pos = w0 + p;
             s_pos[warp] = pos;
             s_n[warp] = done ? -n - 1 : n;
         }
