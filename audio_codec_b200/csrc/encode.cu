@@ -38,13 +38,29 @@ k_transient(const short* __restrict__ pcm, const int* __restrict__ blkOff, const
     const int s = lo, k = g - blkOff[s], nbs = nb[s];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int cmaxAll[8], amaxAll[8];
-    for (int c = 0; c < C && c < 8; ++c) {
+    // a thread owns 8 consecutive samples of each channel (one 16-byte load when the buffer allows), kept in
+    // registers for both passes (up to 4 channels; more: the second pass reads again)
+    const bool vec = (((size_t)pcm) & 15) == 0;
+    uint4 held[4];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        if (c >= C) break;
         const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
+        uint4 v4;
+        if (vec) v4 = __ldg(reinterpret_cast<const uint4*>(p) + tid);
+        else {
+            short t[8];
+            for (int e = 0; e < 8; ++e) t[e] = p[tid * 8 + e];
+            v4 = *reinterpret_cast<uint4*>(t);
+        }
+        if (c < 4) held[c] = v4;
+        const short* q = reinterpret_cast<const short*>(&v4);
         int best = -1, arg = 0;
-        for (int i = tid; i < 1024; i += 128) {
-            int v = p[i];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            int v = q[e];
             v = (v < 0 ? -v : v) & 0x7fff;
-            if (v > best) { best = v; arg = i; }
+            if (v > best) { best = v; arg = tid * 8 + e; }        // first maximum (ascending index)
         }
         for (int o = 16; o; o >>= 1) {
             int ob = __shfl_xor_sync(0xffffffffu, best, o), oa = __shfl_xor_sync(0xffffffffu, arg, o);
@@ -65,11 +81,22 @@ k_transient(const short* __restrict__ pcm, const int* __restrict__ blkOff, const
     const int n = min(nmax, 2048);
     const int nn = min(n, 1024);
     unsigned long long sum = 0;
-    for (int c = 0; c < C && c < 8; ++c) {
-        const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
-        for (int i = tid; i < nn; i += 128) {
-            int v = p[i];
-            sum += (unsigned long long)((v < 0 ? -v : v) & 0x7fff);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        if (c >= C) break;
+        uint4 v4;
+        if (c < 4) v4 = held[c];
+        else {
+            const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
+            short t[8];
+            for (int e = 0; e < 8; ++e) t[e] = p[tid * 8 + e];
+            v4 = *reinterpret_cast<uint4*>(t);
+        }
+        const short* q = reinterpret_cast<const short*>(&v4);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            int v = q[e];
+            if (tid * 8 + e < nn) sum += (unsigned long long)((v < 0 ? -v : v) & 0x7fff);
         }
     }
     for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
