@@ -53,6 +53,8 @@ k_decode_long(const PacDev* __restrict__ dev, double* __restrict__ frames, const
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const T* winAll = t.win_long;
+    const int kl = (lane & 15) + 256 * (lane >> 4), kE = kl + 16 * (lane >> 4), kO = (Q - 1 - kl) + 16 * (1 - (lane >> 4));
+    const int ll = lane * (PER / 2);
     T* Ev = reinterpret_cast<T*>(tb.roots + 256) + (size_t)warp * 2 * MS_TILE;     // DCT-IV output, even indices (skewed)
     T* Ov = Ev + MS_TILE;                                                            // odd indices
     // in the batch's DENSE order (k_hdr: long blocks from the front): the 32 blocks of a 256-byte row of the line array
@@ -82,8 +84,8 @@ k_decode_long(const PacDev* __restrict__ dev, double* __restrict__ frames, const
         for (int r = 0; r < 16; ++r) {
             const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
             const cplx<T> v = cmul(u[r], MsRun<T>::ldc(tb.tw + k));
-            Ev[MS_OSK(k)] = v.x;                   // xv[2k]
-            Ov[MS_OSK(Q - 1 - k)] = -v.y;          // xv[M - 1 - 2k]
+            Ev[kE + 16 * r] = v.x;                 // xv[2k] at MS_OSK(k): k >> 8 = lane >> 4
+            Ov[kO - 16 * r] = -v.y;                // xv[M - 1 - 2k] at MS_OSK(Q - 1 - k): (Q - 1 - k) >> 8 = 1 - (lane >> 4)
         }
         __syncwarp();
         const T* win = winAll + (size_t)shape * 2048;
@@ -91,24 +93,26 @@ k_decode_long(const PacDev* __restrict__ dev, double* __restrict__ frames, const
         for (int i = 0; i < NV; ++i) {
             const int n0 = (i * 32 + lane) * PER;
             T o[PER], tl[PER], ev[L], ov[L];
-            if (n0 < Q) {       // head = 2 xv[Q + n], tail = -2 xv[Q - 1 - n]
-                const int a = (Q + n0) / 2, c = (Q - n0 - PER) / 2;
-                MsRun<T>::ld(Ev + MS_OSK(a), ev);
-                MsRun<T>::ld(Ov + MS_OSK(a), ov);
+            if (i * 32 * PER < Q) {       // (n0 < Q, the same for every lane) head = 2 xv[Q + n], tail = -2 xv[Q - 1 - n]
+                const int A = Q / 2 + i * 16 * PER, C = (Q - PER) / 2 - i * 16 * PER;      // a = (Q + n0) / 2 = A + ll, c = (Q - n0 - PER) / 2 = C - ll
+                const int a = A + 16 * (A >> 8) + ll, c = C + 16 * (C >> 8) - ll;          // MS_OSK: the skew is the same for all lanes
+                MsRun<T>::ld(Ev + a, ev);
+                MsRun<T>::ld(Ov + a, ov);
 #pragma unroll
                 for (int q = 0; q < L; ++q) { o[2 * q] = (T)2 * ev[q]; o[2 * q + 1] = (T)2 * ov[q]; }
-                MsRun<T>::ld(Ev + MS_OSK(c), ev);
-                MsRun<T>::ld(Ov + MS_OSK(c), ov);
+                MsRun<T>::ld(Ev + c, ev);
+                MsRun<T>::ld(Ov + c, ov);
 #pragma unroll
                 for (int q = 0; q < L; ++q) { tl[PER - 1 - 2 * q] = (T)-2 * ev[q]; tl[PER - 2 - 2 * q] = (T)-2 * ov[q]; }
             } else {            // head = -2 xv[3Q - 1 - n], tail = -2 xv[n - Q]
-                const int c = (3 * Q - n0 - PER) / 2, a = (n0 - Q) / 2;
-                MsRun<T>::ld(Ev + MS_OSK(c), ev);
-                MsRun<T>::ld(Ov + MS_OSK(c), ov);
+                const int C = (3 * Q - PER) / 2 - i * 16 * PER, A = i * 16 * PER - Q / 2;
+                const int c = C + 16 * (C >> 8) - ll, a = A + 16 * (A >> 8) + ll;
+                MsRun<T>::ld(Ev + c, ev);
+                MsRun<T>::ld(Ov + c, ov);
 #pragma unroll
                 for (int q = 0; q < L; ++q) { o[PER - 1 - 2 * q] = (T)-2 * ev[q]; o[PER - 2 - 2 * q] = (T)-2 * ov[q]; }
-                MsRun<T>::ld(Ev + MS_OSK(a), ev);
-                MsRun<T>::ld(Ov + MS_OSK(a), ov);
+                MsRun<T>::ld(Ev + a, ev);
+                MsRun<T>::ld(Ov + a, ov);
 #pragma unroll
                 for (int q = 0; q < L; ++q) { tl[2 * q] = (T)-2 * ev[q]; tl[2 * q + 1] = (T)-2 * ov[q]; }
             }

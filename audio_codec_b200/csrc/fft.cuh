@@ -18,6 +18,22 @@ template <typename T> __device__ __forceinline__ cplx<T> cmul(cplx<T> a, cplx<T>
 }
 template <typename T> __device__ __forceinline__ cplx<T> cadd(cplx<T> a, cplx<T> b) { return {a.x + b.x, a.y + b.y}; }
 template <typename T> __device__ __forceinline__ cplx<T> csub(cplx<T> a, cplx<T> b) { return {a.x - b.x, a.y - b.y}; }
+// fp32: one packed instruction per complex add / subtract (sm_100 f32x2 arithmetic: add.rn.f32x2, and a - b as
+// fma.rn.f32x2(b, -1, a): the product is exact, so both are the IEEE results of the scalar forms).  The streaming MDCT
+// kernels are bound by instruction issue, and most of an FFT's instructions are these.
+#ifndef PAC_F32X2
+#define PAC_F32X2 1
+#endif
+#if PAC_F32X2
+template <> __device__ __forceinline__ cplx<float> cadd<float>(cplx<float> a, cplx<float> b) {
+    const float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return {r.x, r.y};
+}
+template <> __device__ __forceinline__ cplx<float> csub<float>(cplx<float> a, cplx<float> b) {
+    const float2 r = __ffma2_rn(make_float2(b.x, b.y), make_float2(-1.0f, -1.0f), make_float2(a.x, a.y));
+    return {r.x, r.y};
+}
+#endif
 // multiply by -j
 template <typename T> __device__ __forceinline__ cplx<T> cmnj(cplx<T> a) { return {a.y, -a.x}; }
 

@@ -127,7 +127,10 @@ template <typename T> struct MsTables {
     cplx<T>* r1;
     cplx<T>* roots;
 };
-template <typename T, int NT, bool EO>
+// MODE folds a power-of-two factor of the transform into the kernel's private copy of the window (exact: the
+// products, and everything linear after them, scale without a rounding): 0 none; 1 forward, w * 2/N (the MDCT's
+// output scale); 2 inverse, the unfolding factors of imdct_sample: +2 w on [0, N/4), -2 w on [N/4, N).
+template <typename T, int NT, bool EO, int MODE = 0>
 __device__ __forceinline__ unsigned char* ms_load_tables(unsigned char* raw, const T* __restrict__ winG,
                                                          const cplx<T>* __restrict__ twG,
                                                          const cplx<T>* __restrict__ rootsG, MsTables<T>& t) {
@@ -137,7 +140,9 @@ __device__ __forceinline__ unsigned char* ms_load_tables(unsigned char* raw, con
     t.r1 = t.tw + Q;
     t.roots = t.r1 + 256;
     for (int i = threadIdx.x; i < N; i += NT) {
-        const T w = winG ? winG[i] : (T)1;
+        T w = winG ? winG[i] : (T)1;
+        if (MODE == 1) w *= (T)2 / (T)N;
+        if (MODE == 2) w *= i < 512 ? (T)2 : (T)-2;
         if (EO) t.win[((i >> 10) * 2 + (i & 1)) * 512 + ((i & 1023) >> 1)] = w;
         else t.win[i] = w;
     }

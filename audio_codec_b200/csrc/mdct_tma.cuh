@@ -69,6 +69,21 @@ template <> struct MtPair<double> {
         a = v.x; b = v.y;
     }
 };
+// (a0 b0, a1 b1): one packed multiply in fp32
+template <typename T> __device__ __forceinline__ void mt_mul2(T a0, T a1, T b0, T b1, T& r0, T& r1) { r0 = a0 * b0; r1 = a1 * b1; }
+#if PAC_F32X2
+template <> __device__ __forceinline__ void mt_mul2<float>(float a0, float a1, float b0, float b1, float& r0, float& r1) {
+    const float2 r = __fmul2_rn(make_float2(a0, a1), make_float2(b0, b1));
+    r0 = r.x; r1 = r.y;
+}
+#endif
+template <typename T> __device__ __forceinline__ void mt_add2(T a0, T a1, T b0, T b1, T& r0, T& r1) { r0 = a0 + b0; r1 = a1 + b1; }
+#if PAC_F32X2
+template <> __device__ __forceinline__ void mt_add2<float>(float a0, float a1, float b0, float b1, float& r0, float& r1) {
+    const float2 r = __fadd2_rn(make_float2(a0, a1), make_float2(b0, b1));
+    r0 = r.x; r1 = r.y;
+}
+#endif
 template <typename T> __device__ __forceinline__ cplx<T> mt_shfl_mirror(cplx<T> v, int lane) {
     cplx<T> r = {__shfl_sync(0xffffffffu, v.x, 31 - lane), __shfl_sync(0xffffffffu, v.y, 31 - lane)};
     return r;
@@ -88,7 +103,7 @@ k_mdct_fwd_tma(const T* __restrict__ x, long long rowStride, int nFrames, int se
     constexpr unsigned BLK_BYTES = M * sizeof(T);
     extern __shared__ __align__(128) unsigned char smem_raw[];
     MsTables<T> tb;
-    unsigned char* p = ms_load_tables<T, W * 32, false>(smem_raw, winG, twG, rootsG, tb);
+    unsigned char* p = ms_load_tables<T, W * 32, false, 1>(smem_raw, winG, twG, rootsG, tb);     // window * 2 / N
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     T* ring = reinterpret_cast<T*>(p) + (size_t)warp * (MT_RING * MT_SLOT);
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(reinterpret_cast<T*>(p) + (size_t)W * (MT_RING * MT_SLOT)) +
@@ -99,7 +114,6 @@ k_mdct_fwd_tma(const T* __restrict__ x, long long rowStride, int nFrames, int se
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    const T scale = (T)2 / (T)N;
     const T* W0 = tb.win;            // window over samples [0, M) of the frame, natural order
     const T* W1 = tb.win + M;        // [M, N)
     unsigned used = 0;               // blocks this warp has sent through the ring so far (slot and phase follow)
@@ -143,11 +157,15 @@ k_mdct_fwd_tma(const T* __restrict__ x, long long rowStride, int nFrames, int se
                     MtPair<T>::ld(W1 + 512 + 2 * m, w1bx, w1by);
                 }
                 // point m (< 256): v[2n] = -x[i0] - x[i1], v[M-1-2n] = x[i2] - x[i3]
-                const T a0 = b1ay * w1ay, a1 = b1bx * w1bx, a2 = b0ay * w0ay, a3 = b0bx * w0bx;
+                // the eight products are the four pairs times their window pairs
+                T a0, a1, a2, a3, c0, c1, c2, c3;
+                mt_mul2<T>(b0ax, b0ay, w0ax, w0ay, c0, a2);
+                mt_mul2<T>(b0bx, b0by, w0bx, w0by, a3, c1);
+                mt_mul2<T>(b1ax, b1ay, w1ax, w1ay, c2, a0);
+                mt_mul2<T>(b1bx, b1by, w1bx, w1by, a1, c3);
                 cplx<T> t = {-a0 - a1, a2 - a3};
                 u[i] = cmul(t, MsRun<T>::ldc(tb.tw + m));
                 // point 511 - m (>= 256): v[2n] = x[i0] - x[i1], v[M-1-2n] = -x[i2] - x[i3]
-                const T c0 = b0ax * w0ax, c1 = b0by * w0by, c2 = b1ax * w1ax, c3 = b1by * w1by;
                 cplx<T> s = {c0 - c1, -c2 - c3};
                 s = cmul(s, MsRun<T>::ldc(tb.tw + (Q - 1 - m)));
                 u[15 - i] = mt_shfl_mirror(s, lane);      // point 511 - m' of lane 31 - l = l + 32 (15 - i)
@@ -159,13 +177,15 @@ k_mdct_fwd_tma(const T* __restrict__ x, long long rowStride, int nFrames, int se
                 mt_bulk_load(ring + (u2 % MT_RING) * MT_SLOT, src + (long long)(j + 2) * M, BLK_BYTES, &bars[u2 % MT_RING]);
             }
             T* tile = B0;                                 // exchange tile, then the natural-order output tile
+#ifndef MT_EXPERIMENT_NOFFT                              // (experiment: the pipeline without the transform = its copy ceiling)
             warp_fft512<T>(u, tile, tb, lane);
+#endif
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
                 const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
                 const cplx<T> y = cmul(u[r], MsRun<T>::ldc(tb.tw + k));
-                tile[2 * k] = scale * y.x;
-                tile[M - 1 - 2 * k] = -scale * y.y;
+                tile[2 * k] = y.x;                        // the 2 / N came in with the window
+                tile[M - 1 - 2 * k] = -y.y;
             }
             mt_fence_async();            // generic-proxy writes visible to the bulk-copy engine
             __syncwarp();
@@ -191,7 +211,7 @@ k_imdct_ola_tma(const T* __restrict__ X, int nFrames, int seg, int segsPerRow, l
     constexpr unsigned BLK_BYTES = M * sizeof(T);
     extern __shared__ __align__(128) unsigned char smem_raw[];
     MsTables<T> tb;
-    unsigned char* p = ms_load_tables<T, W * 32, false>(smem_raw, winG, twG, rootsG, tb);
+    unsigned char* p = ms_load_tables<T, W * 32, false, 2>(smem_raw, winG, twG, rootsG, tb);     // window * (+-2)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     T* ring = reinterpret_cast<T*>(p) + (size_t)warp * (MT_RING * MT_SLOT);
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(reinterpret_cast<T*>(p) + (size_t)W * (MT_RING * MT_SLOT)) +
@@ -203,6 +223,8 @@ k_imdct_ola_tma(const T* __restrict__ X, int nFrames, int seg, int segsPerRow, l
     }
     __syncwarp();
     const int nOutRow = nFrames + 1;
+    const int kl = (lane & 15) + 256 * (lane >> 4), kE = kl + 16 * (lane >> 4), kO = (Q - 1 - kl) + 16 * (1 - (lane >> 4));
+    const int ll = lane * (PER / 2);
     unsigned used = 0;
     for (long long unit = (long long)blockIdx.x * W + warp; unit < nUnits; unit += (long long)gridDim.x * W) {
         const long long row = unit / segsPerRow;
@@ -255,8 +277,8 @@ k_imdct_ola_tma(const T* __restrict__ X, int nFrames, int seg, int segsPerRow, l
                 for (int r = 0; r < 16; ++r) {
                     const int k = (lane & 15) + 16 * r + 256 * (lane >> 4);
                     const cplx<T> v = cmul(u[r], MsRun<T>::ldc(tb.tw + k));
-                    Ev[MS_OSK(k)] = v.x;                   // xv[2k]
-                    Ov[MS_OSK(Q - 1 - k)] = -v.y;          // xv[M - 1 - 2k]
+                    Ev[kE + 16 * r] = v.x;                 // xv[2k] at MS_OSK(k): k >> 8 = lane >> 4
+                    Ov[kO - 16 * r] = -v.y;                // xv[M - 1 - 2k] at MS_OSK(Q - 1 - k): (Q - 1 - k) >> 8 = 1 - (lane >> 4)
                 }
             }
             __syncwarp();
@@ -269,36 +291,44 @@ k_imdct_ola_tma(const T* __restrict__ X, int nFrames, int seg, int segsPerRow, l
                 for (int e = 0; e < PER; ++e) { o[e] = (T)0; tl[e] = (T)0; }
                 if (have) {
                     T ev[L], ov[L];
-                    if (n0 < Q) {       // head = 2 xv[Q + n], tail = -2 xv[Q - 1 - n]
-                        const int a = (Q + n0) / 2, c = (Q - n0 - PER) / 2;
-                        MsRun<T>::ld(Ev + MS_OSK(a), ev);
-                        MsRun<T>::ld(Ov + MS_OSK(a), ov);
+                    if (i * 32 * PER < Q) {       // (n0 < Q, the same for every lane) head = 2 xv[Q + n], tail = -2 xv[Q - 1 - n] (the factors are in the window copy)
+                        const int A = Q / 2 + i * 16 * PER, C = (Q - PER) / 2 - i * 16 * PER;      // a = (Q + n0) / 2 = A + ll, c = (Q - n0 - PER) / 2 = C - ll
+                        const int a = A + 16 * (A >> 8) + ll, c = C + 16 * (C >> 8) - ll;          // MS_OSK: the skew is the same for all lanes
+                        MsRun<T>::ld(Ev + a, ev);
+                        MsRun<T>::ld(Ov + a, ov);
 #pragma unroll
-                        for (int q = 0; q < L; ++q) { o[2 * q] = (T)2 * ev[q]; o[2 * q + 1] = (T)2 * ov[q]; }
-                        MsRun<T>::ld(Ev + MS_OSK(c), ev);
-                        MsRun<T>::ld(Ov + MS_OSK(c), ov);
+                        for (int q = 0; q < L; ++q) { o[2 * q] = ev[q]; o[2 * q + 1] = ov[q]; }
+                        MsRun<T>::ld(Ev + c, ev);
+                        MsRun<T>::ld(Ov + c, ov);
 #pragma unroll
-                        for (int q = 0; q < L; ++q) { tl[PER - 1 - 2 * q] = (T)-2 * ev[q]; tl[PER - 2 - 2 * q] = (T)-2 * ov[q]; }
+                        for (int q = 0; q < L; ++q) { tl[PER - 1 - 2 * q] = ev[q]; tl[PER - 2 - 2 * q] = ov[q]; }
                     } else {            // head = -2 xv[3Q - 1 - n], tail = -2 xv[n - Q]
-                        const int c = (3 * Q - n0 - PER) / 2, a = (n0 - Q) / 2;
-                        MsRun<T>::ld(Ev + MS_OSK(c), ev);
-                        MsRun<T>::ld(Ov + MS_OSK(c), ov);
+                        const int C = (3 * Q - PER) / 2 - i * 16 * PER, A = i * 16 * PER - Q / 2;
+                        const int c = C + 16 * (C >> 8) - ll, a = A + 16 * (A >> 8) + ll;
+                        MsRun<T>::ld(Ev + c, ev);
+                        MsRun<T>::ld(Ov + c, ov);
 #pragma unroll
-                        for (int q = 0; q < L; ++q) { o[PER - 1 - 2 * q] = (T)-2 * ev[q]; o[PER - 2 - 2 * q] = (T)-2 * ov[q]; }
-                        MsRun<T>::ld(Ev + MS_OSK(a), ev);
-                        MsRun<T>::ld(Ov + MS_OSK(a), ov);
+                        for (int q = 0; q < L; ++q) { o[PER - 1 - 2 * q] = ev[q]; o[PER - 2 - 2 * q] = ov[q]; }
+                        MsRun<T>::ld(Ev + a, ev);
+                        MsRun<T>::ld(Ov + a, ov);
 #pragma unroll
-                        for (int q = 0; q < L; ++q) { tl[2 * q] = (T)-2 * ev[q]; tl[2 * q + 1] = (T)-2 * ov[q]; }
+                        for (int q = 0; q < L; ++q) { tl[2 * q] = ev[q]; tl[2 * q + 1] = ov[q]; }
                     }
                     const uint4 w0 = *reinterpret_cast<const uint4*>(tb.win + n0);
                     const uint4 w1 = *reinterpret_cast<const uint4*>(tb.win + M + n0);
                     const T* wh = reinterpret_cast<const T*>(&w0);
                     const T* wt = reinterpret_cast<const T*>(&w1);
 #pragma unroll
-                    for (int e = 0; e < PER; ++e) { o[e] *= wh[e]; tl[e] *= wt[e]; }
+                    for (int e = 0; e < PER; e += 2) {
+                        mt_mul2<T>(o[e], o[e + 1], wh[e], wh[e + 1], o[e], o[e + 1]);
+                        mt_mul2<T>(tl[e], tl[e + 1], wt[e], wt[e + 1], tl[e], tl[e + 1]);
+                    }
                 }
 #pragma unroll
-                for (int e = 0; e < PER; ++e) { o[e] += tail[i * PER + e]; tail[i * PER + e] = tl[e]; }
+                for (int e = 0; e < PER; e += 2) {
+                    mt_add2<T>(o[e], o[e + 1], tail[i * PER + e], tail[i * PER + e + 1], o[e], o[e + 1]);
+                    tail[i * PER + e] = tl[e]; tail[i * PER + e + 1] = tl[e + 1];
+                }
                 if (f >= b0) *reinterpret_cast<uint4*>(dst + (long long)f * M + n0) = *reinterpret_cast<uint4*>(o);
             }
             __syncwarp();
