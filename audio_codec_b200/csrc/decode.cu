@@ -191,6 +191,9 @@ k_hdr(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, CbHd
 #ifndef DQ_NT
 #define DQ_NT 128
 #endif
+#ifndef DQ_SORT
+#define DQ_SORT 1
+#endif
 #ifndef DQ_MINB
 #define DQ_MINB 7          // 72 registers (96 when free): seven CTAs per SM (measured 5 / 6 / 7 / 8: 32.0 / 29.7 / 29.2 / 31.3 ms decode)
 #endif
@@ -202,10 +205,54 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
     for (int i = threadIdx.x; i < PAC_PVQ_LMAX + 2; i += DQ_NT) s_off[i] = dev->pvqRowOff[i];
     __syncthreads();
     const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
-    const int pos = chunk * DQ_NT + threadIdx.x;
     const int nLong = counts[0], nShort = counts[1];
+    const int nBL = dev->longBands.nBands, nBS = dev->shortBands.nBands;
+    // The 128 blocks of the CTA are dealt to its threads in the order of this band's bit allocation (a counting sort
+    // in shared memory): the lanes of a warp then walk trees of similar size.  A thread keeps the workspace of its own
+    // place; only the block it decodes - and so where its lines go - is permuted.
+#if DQ_SORT
+    __shared__ int s_cnt[3][34];
+    __shared__ unsigned char s_order[DQ_NT];
+    {
+        // The dense order puts long blocks at the front of the batch and transient blocks at its back; the tile that
+        // holds the boundary has both (and the unused places between them).  Blocks are permuted WITHIN their kind's
+        // part of the tile only: a workspace column then serves one kind in every band's CTA (the two kinds lay out
+        // their bands' rows differently).
+        const int tile0 = chunk * DQ_NT, pos0 = tile0 + threadIdx.x;
+        const int gap0 = min(max(nLong - tile0, 0), DQ_NT), tr0 = min(max(nCb - nShort - tile0, 0), DQ_NT);   // long [0, gap0), unused [gap0, tr0), transient [tr0, ..)
+        const int cls = threadIdx.x < gap0 ? 0 : (threadIdx.x < tr0 ? 1 : 2);
+        int key = 33;                                          // nothing to do: last of its part
+        if (cls != 1 && pos0 < nCb && !(q >= nBL && cls == 0)) {
+            const CbHdr* h0 = hdrs + perm[pos0];
+            const unsigned char fl0 = h0->flags;
+            if (fl0 & 0x80u) {
+                const bool cur0 = (fl0 >> 1) & 1;
+                const int nB0 = cur0 ? nBS : nBL;
+                if (q < (cur0 ? PAC_SUBFRAMES * nB0 : nB0)) {
+                    const int f0 = q / nB0, b0 = nB0 - 1 - (q - f0 * nB0);
+                    key = min((int)h0->ba[f0 * nB0 + b0], 32);
+                }
+            }
+        }
+        if (threadIdx.x < 3 * 34) (&s_cnt[0][0])[threadIdx.x] = 0;
+        __syncthreads();
+        const int rank = atomicAdd(&s_cnt[cls][key], 1);
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            int acc = threadIdx.x == 0 ? 0 : (threadIdx.x == 1 ? gap0 : tr0);
+            for (int j = 0; j < 34; ++j) { const int c = s_cnt[threadIdx.x][j]; s_cnt[threadIdx.x][j] = acc; acc += c; }
+        }
+        __syncthreads();
+        s_order[s_cnt[cls][key] + rank] = (unsigned char)threadIdx.x;
+        __syncthreads();
+    }
+    const int wsPos = chunk * DQ_NT + threadIdx.x;             // workspace: this thread's own place
+    const int pos = chunk * DQ_NT + s_order[threadIdx.x];      // the block it decodes
+#else
+    const int pos = chunk * DQ_NT + threadIdx.x, wsPos = pos;
+#endif
     if (pos >= nCb || (pos >= nLong && pos < nCb - nShort)) return;
-    if (q >= dev->longBands.nBands && pos < nLong) return;
+    if (q >= nBL && pos < nLong) return;
     const int local = perm[pos];
     CbHdr* h = hdrs + local;
     const unsigned char fl = h->flags;
@@ -234,7 +281,7 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
         all += c;
     }
     base += f * all;                                           // <= 2 * 1024 in total for either frame type
-    double* wsA = ws + ((size_t)(pos >> 5) * (2 * PRE_WS_PER_CB) + (size_t)base) * 32 + (pos & 31);
+    double* wsA = ws + ((size_t)(wsPos >> 5) * (2 * PRE_WS_PER_CB) + (size_t)base) * 32 + (wsPos & 31);
     double* wsB = wsA + (size_t)PRE_WS_PER_CB * 32;
     int nBytes;
     long long bit0;
