@@ -320,6 +320,9 @@ __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, i
     *cap = c0;
     *wbase = wb + f * wall;
 }
+#ifndef PQ_SORT
+#define PQ_SORT 1
+#endif
 #ifndef PQ_MINB
 #define PQ_MINB 6          // 80 registers: the compiler takes 158 when free, three CTAs per SM instead of six (measured: 53.6 -> 50.9 ms encode)
 #endif
@@ -330,10 +333,47 @@ k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict
     for (int i = threadIdx.x; i < PAC_PVQ_LMAX + 2; i += PQ_NT) s_off[i] = dev->pvqRowOff[i];
     __syncthreads();
     const int q = blockIdx.x / nChunks, chunk = blockIdx.x - q * nChunks;
-    const int pos = chunk * PQ_NT + threadIdx.x;
     const int nLong = a.counts[0], nShort = a.counts[1];
+    const int nBL = dev->longBands.nBands, nBS = dev->shortBands.nBands;
+    // As k_dequant: the 128 blocks of the CTA are dealt to its threads in the order of this band's bit allocation, within
+    // the long / transient parts of the tile; a thread keeps the workspace column of its own place, the block it
+    // quantises (its lines, its word buffer) is permuted.
+#if PQ_SORT
+    __shared__ int s_cnt[3][34];
+    __shared__ unsigned char s_order[PQ_NT];
+    {
+        const int tile0 = chunk * PQ_NT, pos0 = tile0 + threadIdx.x;
+        const int gap0 = min(max(nLong - tile0, 0), PQ_NT), tr0 = min(max(a.nBatch - nShort - tile0, 0), PQ_NT);
+        const int cls = threadIdx.x < gap0 ? 0 : (threadIdx.x < tr0 ? 1 : 2);
+        int key = 33;                                          // nothing to do: last of its part
+        if (cls != 1 && pos0 < a.nBatch && !(q >= nBL && cls == 0)) {
+            const EncPre* h0 = a.pre + a.perm[pos0];
+            const bool cur0 = (h0->flags >> 1) & 1;
+            const int nB0 = cur0 ? nBS : nBL;
+            if (q < (cur0 ? PAC_SUBFRAMES * nB0 : nB0)) {
+                const int f0 = q / nB0, b0 = nB0 - 1 - (q - f0 * nB0);
+                key = min((int)h0->ba[f0 * nB0 + b0], 32);
+            }
+        }
+        if (threadIdx.x < 3 * 34) (&s_cnt[0][0])[threadIdx.x] = 0;
+        __syncthreads();
+        const int rank = atomicAdd(&s_cnt[cls][key], 1);
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            int acc = threadIdx.x == 0 ? 0 : (threadIdx.x == 1 ? gap0 : tr0);
+            for (int j = 0; j < 34; ++j) { const int c = s_cnt[threadIdx.x][j]; s_cnt[threadIdx.x][j] = acc; acc += c; }
+        }
+        __syncthreads();
+        s_order[s_cnt[cls][key] + rank] = (unsigned char)threadIdx.x;
+        __syncthreads();
+    }
+    const int wsPos = chunk * PQ_NT + threadIdx.x;
+    const int pos = chunk * PQ_NT + s_order[threadIdx.x];
+#else
+    const int pos = chunk * PQ_NT + threadIdx.x, wsPos = pos;
+#endif
     if (pos >= a.nBatch || (pos >= nLong && pos < a.nBatch - nShort)) return;
-    if (q >= dev->longBands.nBands && pos < nLong) return;
+    if (q >= nBL && pos < nLong) return;
     EncPre* h = a.pre + a.perm[pos];
     const bool cur = (h->flags >> 1) & 1;
     const PacBands& bands = cur ? dev->shortBands : dev->longBands;
@@ -348,11 +388,12 @@ k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict
     epre_band_layout(bands, f, b, &base, &cap, &wbase);
     int k = 0;
     if (env) for (int j = 0; j < b; ++j) k += bands.omitted[j] ? 1 : 0;
-    const size_t grp = (size_t)(pos >> 5), ln = (size_t)(pos & 31);
+    const size_t grp = (size_t)(pos >> 5), ln = (size_t)(pos & 31);               // the block: lines in, words out
+    const size_t wgrp = (size_t)(wsPos >> 5), wln = (size_t)(wsPos & 31);         // the thread's own workspace column
     const double* x = a.preLines + epre_line_index(pos, f * PAC_HALF_SHORT + bands.lower[b]);
-    double* wsA = ws + (grp * (2 * EPRE_WS_PER_CB) + (size_t)base) * 32 + ln;
+    double* wsA = ws + (wgrp * (2 * EPRE_WS_PER_CB) + (size_t)base) * 32 + wln;
     double* wsB = wsA + (size_t)EPRE_WS_PER_CB * 32;
-    int* y = yws + (grp * EPRE_WS_PER_CB + (size_t)base) * 32 + ln;
+    int* y = yws + (wgrp * EPRE_WS_PER_CB + (size_t)base) * 32 + wln;
     unsigned* w = words + (grp * EPRE_WORDS_PER_CB + (size_t)wbase) * 32 + ln;
     PvqTab pt = {dev->pvqN, s_off, dev->log2tab, dev->pvqKW, dev->thetaTab};
     int werr = 0;
