@@ -212,7 +212,7 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
     // place; only the block it decodes - and so where its lines go - is permuted.
 #if DQ_SORT
     __shared__ int s_cnt[3][34];
-    __shared__ unsigned char s_order[DQ_NT];
+    __shared__ unsigned short s_order[DQ_NT];
     {
         // The dense order puts long blocks at the front of the batch and transient blocks at its back; the tile that
         // holds the boundary has both (and the unused places between them).  Blocks are permuted WITHIN their kind's
@@ -243,7 +243,7 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
             for (int j = 0; j < 34; ++j) { const int c = s_cnt[threadIdx.x][j]; s_cnt[threadIdx.x][j] = acc; acc += c; }
         }
         __syncthreads();
-        s_order[s_cnt[cls][key] + rank] = (unsigned char)threadIdx.x;
+        s_order[s_cnt[cls][key] + rank] = (unsigned short)threadIdx.x;
         __syncthreads();
     }
     const int wsPos = chunk * DQ_NT + threadIdx.x;             // workspace: this thread's own place
@@ -303,6 +303,40 @@ k_dequant(const PacDev* __restrict__ dev, DecArgs a, long long cbBase, int nCb, 
 #ifndef DEC_PRE_MINB
 #define DEC_PRE_MINB 4
 #endif
+// The eight short frames of a transient block behind k_dequant, ONE PER WARP, all at once (run one after the other on
+// the whole CTA a transient block took 73 us: a 64-point FFT keeps 8 of 256 threads busy).  Each warp: its 128 lines,
+// scale, IMDCT (the CTA FFT code with NT = 32 on the warp's own buffers; its barriers are unconditional, so the eight
+// warps pass them together), sine window.  The frames overlap by half: even frames add into y first, then odd ones -
+// every sample gets the same two addends as in frame order (coder/pacfile.py:258-287).
+template <typename T>
+__device__ __forceinline__ void decode_short_frames_pre(const PacDev* __restrict__ dev, const DecSmem& S,
+                                                        const CbHdr* __restrict__ pre, const double* __restrict__ preLines) {
+    constexpr int N = PAC_NSHORT, H = N / 2, Q = N / 4;
+    const int sf = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const PacTables<T>& t = psy_tabs<T>(dev);
+    const cplx<T>* tw = reinterpret_cast<const cplx<T>*>(t.tw_mdct_short);
+    const cplx<T>* roots = reinterpret_cast<const cplx<T>*>(t.tw_fft[0]);
+    double* lines = S.lines + H * sf;                                     // [128]
+    cplx<T>* fbuf = reinterpret_cast<cplx<T>*>(S.wsA + 256 * sf);         // [64] complex
+    T* v = reinterpret_cast<T*>(S.wsA + 256 * sf + 128);                  // [128]
+    for (int i = lane; i < H; i += 32) lines[i] = preLines[pre_line_index(pre->p, sf * H + i)];
+    const double inv = 1.0 / (double)(1 << pre->scale[sf]);
+    __syncthreads();
+    imdct_pre<T, N, 1, 32, double>(lines, inv, tw, fbuf, lane);
+    __syncthreads();
+    cta_fft<T, Q, 1, 32>(fbuf, roots, lane);
+    mdct_post<T, N, 1, 32>(fbuf, tw, (T)1, v, lane);
+    __syncthreads();
+    const T* w = t.win_short + PAC_WIN_SINE * N;
+    const int yOff = 448 + 128 * sf;
+#pragma unroll
+    for (int ph = 0; ph < 2; ++ph) {
+        if ((sf & 1) == ph)
+            for (int i = lane; i < N; i += 32) S.y[yOff + i] += (double)(w[i] * imdct_sample<T, N>(v, i));
+        __syncthreads();
+    }
+}
+
 template <typename T, bool PRE>
 __global__ void __launch_bounds__(DEC_NT, PRE ? DEC_PRE_MINB : 3)
 k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ preAll, const double* __restrict__ preLines,
@@ -345,6 +379,8 @@ k_decode(const PacDev* __restrict__ dev, DecArgs a, const CbHdr* __restrict__ pr
         if (!cur) {
             int shape = (last && nxt) ? PAC_WIN_STARTSTOP : last ? PAC_WIN_STOP : nxt ? PAC_WIN_START : PAC_WIN_SINE;
             decode_frame<PAC_NLONG, T>(dev, S, recBits, shape, 0, a.err, pre, preLines, local, 0);
+        } else if (PRE && DEC_NT == 32 * PAC_SUBFRAMES) {
+            decode_short_frames_pre<T>(dev, S, pre, preLines);
         } else {
             for (int sf = 0; sf < PAC_SUBFRAMES; ++sf)
                 decode_frame<PAC_NSHORT, T>(dev, S, recBits, PAC_WIN_SINE, 448 + 128 * sf, a.err, pre, preLines, local, sf);

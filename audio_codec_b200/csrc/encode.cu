@@ -304,7 +304,7 @@ k_bitalloc(const PacDev* __restrict__ dev, EncArgs a) {
 // of the dense order; CTAs are ordered widest band first.  Slot q of a long block is band nB-1-q; of
 // a transient block, sub-frame q / 6, band 5 - q % 6.
 #ifndef PQ_NT
-#define PQ_NT 128
+#define PQ_NT 256         // the tile the bit-allocation sort runs over (measured 128 / 256 / 384 / 768: 8.5 / 8.07 / 8.02 / 8.18 ms)
 #endif
 __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, int b, int* base, int* cap, int* wbase) {
     int c0 = 1, bs = 0, all = 0, wb = 0, wall = 0;
@@ -324,7 +324,7 @@ __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, i
 #define PQ_SORT 1
 #endif
 #ifndef PQ_MINB
-#define PQ_MINB 6          // 80 registers: the compiler takes 158 when free, three CTAs per SM instead of six (measured: 53.6 -> 50.9 ms encode)
+#define PQ_MINB 3          // 80 registers: the compiler takes 158 when free (half the threads per SM; measured: 53.6 -> 50.9 ms encode)
 #endif
 __global__ void __launch_bounds__(PQ_NT, PQ_MINB)
 k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict__ ws, int* __restrict__ yws,
@@ -340,7 +340,7 @@ k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict
     // quantises (its lines, its word buffer) is permuted.
 #if PQ_SORT
     __shared__ int s_cnt[3][34];
-    __shared__ unsigned char s_order[PQ_NT];
+    __shared__ unsigned short s_order[PQ_NT];
     {
         const int tile0 = chunk * PQ_NT, pos0 = tile0 + threadIdx.x;
         const int gap0 = min(max(nLong - tile0, 0), PQ_NT), tr0 = min(max(a.nBatch - nShort - tile0, 0), PQ_NT);
@@ -364,7 +364,7 @@ k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict
             for (int j = 0; j < 34; ++j) { const int c = s_cnt[threadIdx.x][j]; s_cnt[threadIdx.x][j] = acc; acc += c; }
         }
         __syncthreads();
-        s_order[s_cnt[cls][key] + rank] = (unsigned char)threadIdx.x;
+        s_order[s_cnt[cls][key] + rank] = (unsigned short)threadIdx.x;
         __syncthreads();
     }
     const int wsPos = chunk * PQ_NT + threadIdx.x;
