@@ -481,7 +481,7 @@ extern "C" int pac_decode_plan(pac_ctx* ctx, const unsigned char* d_pac, const l
 int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off,
                                int n_streams, short* d_pcm, long long pcm_capacity, long long* h_pcm_off,
                                int* h_err, void* stream, const int* chunks, int n_chunks, cudaEvent_t* chunkEv,
-                               cudaStream_t copyStream, short* h_copy_dst) {
+                               cudaStream_t copyStream, short* h_copy_dst, const int* h_counts) {
     if (!ctx || !h_stream_off || !h_pcm_off) return PAC_ERR_ARG;
     if (n_streams <= 0) return 0;
     if (!d_pac || !d_pcm) return PAC_ERR_ARG;
@@ -490,8 +490,11 @@ int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const l
     PAC_CHECK(cudaSetDevice(ctx->device));
     const int C = ctx->cfg.n_channels, S = n_streams;
     std::vector<long long> cbOff;
-    int rc = walk_streams(ctx, d_pac, h_stream_off, S, st, cbOff, nullptr, nullptr);
-    if (rc) return rc;
+    int rc = 0;
+    if (h_counts) {                                        // the caller has walked the streams already (pac_decode_count_async)
+        cbOff.assign(S + 1, 0);
+        for (int s = 0; s < S; ++s) cbOff[s + 1] = cbOff[s] + h_counts[s] - h_counts[s] % C;
+    } else if ((rc = walk_streams(ctx, d_pac, h_stream_off, S, st, cbOff, nullptr, nullptr))) return rc;
     std::vector<long long> pcmOff(S + 1, 0);
     for (int s = 0; s < S; ++s) pcmOff[s + 1] = pcmOff[s] + ((cbOff[s + 1] - cbOff[s]) / C + 1) * 1024 * C;
     memcpy(h_pcm_off, pcmOff.data(), (S + 1) * sizeof(long long));
@@ -619,7 +622,7 @@ extern "C" int pac_decode_streams(pac_ctx* ctx, const unsigned char* d_pac, cons
                                   int n_streams, short* d_pcm, long long pcm_capacity, long long* h_pcm_off,
                                   int* h_err, void* stream) {
     return pac_decode_streams_chunked(ctx, d_pac, h_stream_off, n_streams, d_pcm, pcm_capacity, h_pcm_off, h_err, stream,
-                                      nullptr, 0, nullptr, nullptr, nullptr);
+                                      nullptr, 0, nullptr, nullptr, nullptr, nullptr);
 }
 
 #ifdef PAC_PHASE_TIMING

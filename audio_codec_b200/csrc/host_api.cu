@@ -152,8 +152,12 @@ extern "C" int pac_decode_host(pac_ctx* ctx, const unsigned char* h_pac, const l
     // finished chunk down while the next ones decode
     PAC_CHECK(cudaStreamSynchronize(ctx->cp[1]));         // the staging buffer may still be draining from the last call
     int errAll = 0;
+    // the plan above has counted the channel-blocks of every stream: hand the counts on instead of walking again
+    std::vector<int> counts(n_streams);
+    for (int s = 0; s < n_streams; ++s)
+        counts[s] = (int)(((h_pcm_off[s + 1] - h_pcm_off[s]) / (1024LL * ctx->cfg.n_channels) - 1) * ctx->cfg.n_channels);
     rc = pac_decode_streams_chunked(ctx, (const unsigned char*)dIn, off.data(), n_streams, (short*)dOut, totalAll, h_pcm_off,
-                                    &errAll, stream, cb.data(), nChunks, ctx->chunkEv, ctx->cp[1], h_pcm);
+                                    &errAll, stream, cb.data(), nChunks, ctx->chunkEv, ctx->cp[1], h_pcm, counts.data());
     if (rc != 0 && rc != PAC_ERR_SOFT) return rc;
     const int soft = rc == PAC_ERR_SOFT;
     PAC_CHECK(cudaStreamSynchronize(ctx->cp[1]));

@@ -60,4 +60,4 @@ int pac_window_table(pac_ctx* ctx, int kind, int N, int Ns, double alpha, const 
 int pac_decode_streams_chunked(pac_ctx* ctx, const unsigned char* d_pac, const long long* h_stream_off, int n_streams,
                                short* d_pcm, long long pcm_capacity, long long* h_pcm_off, int* h_err, void* stream,
                                const int* chunks, int n_chunks, cudaEvent_t* chunkEv, cudaStream_t copyStream,
-                               short* h_copy_dst);
+                               short* h_copy_dst, const int* h_counts);
