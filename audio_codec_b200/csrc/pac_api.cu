@@ -407,6 +407,8 @@ extern "C" int pac_create(int device, const pac_config* cfg, pac_ctx** out) {
     if (!rc) rc = make_numeric_tables<float>(c, &h.f);
     if (!rc) rc = make_psy(c, PAC_HALF_LONG, &h.barkLong, &h.threshLong, &h.fftFreqLong, &h.fftNormLong);
     if (!rc) rc = make_psy(c, PAC_HALF_SHORT, &h.barkShort, &h.threshShort, &h.fftFreqShort, &h.fftNormShort);
+    h.fftValLong = 1.0 / (PAC_NLONG * (1.0 / cfg->sample_rate));     // as make_psy
+    h.fftValShort = 1.0 / (PAC_NSHORT * (1.0 / cfg->sample_rate));
     for (int w = 0; w < 2 && !rc; ++w) {          // band of every MDCT line
         const PacBands& bd = w ? h.shortBands : h.longBands;
         std::vector<unsigned char> lb(w ? PAC_HALF_SHORT : PAC_HALF_LONG, 0);

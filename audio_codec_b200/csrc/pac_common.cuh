@@ -67,6 +67,8 @@ struct PacDev {
     const unsigned char* lineBandShort;  // [128]
     double fftNormLong;        // 4/(N^2 mean(hanning(N)^2))
     double fftNormShort;
+    double fftValLong;         // rfftfreq spacing 1 / (N (1 / fs)): fftFreq[k] = k * val (the same product the table holds)
+    double fftValShort;
     // PVQ codebook sizes N(L,K), rows L = 0..PAC_PVQ_LMAX, each row up to the first
     // entry exceeding 2^32 (inclusive); rows 0..3 are closed-form and empty here.
     const unsigned long long* pvqN;
