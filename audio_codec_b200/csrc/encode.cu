@@ -20,62 +20,56 @@
 #include "pac_api.h"
 
 // ---------------------------------------------------------------- transient detector
-// One CTA (128 threads) per PCM block, all channels.  Exact integer form of
+// One WARP per PCM block, all channels (4 blocks per CTA; no CTA barrier).  Exact integer form of
 // mymax/avg > 4.5 with avg = mean(|x[:, :n]|), n = min(max_c(argmax_c)+500, 2048):
 //   2*cmax_c*(C*n) > 9*sum|c|   (the second half of the look-ahead is always zero).
-__global__ void __launch_bounds__(128)
+// A lane owns 32 consecutive samples of each channel (four 16-byte loads when the buffer allows), kept in registers
+// for both passes (the first 2 channels; further ones are read again in the second pass).
+#define TR_WARPS 4
+__global__ void __launch_bounds__(TR_WARPS * 32)
 k_transient(const short* __restrict__ pcm, const int* __restrict__ blkOff, const int* __restrict__ nb, int nStreams,
-            int C, unsigned char* __restrict__ det) {
-    __shared__ int s_max[8][4], s_arg[8][4];
-    __shared__ unsigned long long s_sum[4];
-    __shared__ int s_n;
-    const int g = blockIdx.x;                 // global PCM block index
+            int C, int totBlk, unsigned char* __restrict__ det) {
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * TR_WARPS + (threadIdx.x >> 5);     // global PCM block index
+    if (g >= totBlk) return;
     int lo = 0, hi = nStreams;                // stream with blkOff[s] <= g < blkOff[s+1]
     while (hi - lo > 1) {
         int mid = (lo + hi) >> 1;
         if (blkOff[mid] <= g) lo = mid; else hi = mid;
     }
     const int s = lo, k = g - blkOff[s], nbs = nb[s];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int cmaxAll[8], amaxAll[8];
-    // a thread owns 8 consecutive samples of each channel (one 16-byte load when the buffer allows), kept in
-    // registers for both passes (up to 4 channels; more: the second pass reads again)
     const bool vec = (((size_t)pcm) & 15) == 0;
-    uint4 held[4];
+    uint4 held[2][4];
+    int cmaxAll[8];
+    int nmax = 0;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         if (c >= C) break;
         const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
-        uint4 v4;
-        if (vec) v4 = __ldg(reinterpret_cast<const uint4*>(p) + tid);
-        else {
-            short t[8];
-            for (int e = 0; e < 8; ++e) t[e] = p[tid * 8 + e];
-            v4 = *reinterpret_cast<uint4*>(t);
-        }
-        if (c < 4) held[c] = v4;
-        const short* q = reinterpret_cast<const short*>(&v4);
         int best = -1, arg = 0;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            int v = q[e];
-            v = (v < 0 ? -v : v) & 0x7fff;
-            if (v > best) { best = v; arg = tid * 8 + e; }        // first maximum (ascending index)
+        for (int j = 0; j < 4; ++j) {
+            uint4 v4;
+            if (vec) v4 = __ldg(reinterpret_cast<const uint4*>(p) + lane * 4 + j);
+            else {
+                short t[8];
+                for (int e = 0; e < 8; ++e) t[e] = p[lane * 32 + j * 8 + e];
+                v4 = *reinterpret_cast<uint4*>(t);
+            }
+            if (c < 2) held[c][j] = v4;
+            const short* q = reinterpret_cast<const short*>(&v4);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                int v = q[e];
+                v = (v < 0 ? -v : v) & 0x7fff;
+                if (v > best) { best = v; arg = lane * 32 + j * 8 + e; }      // first maximum (ascending index)
+            }
         }
         for (int o = 16; o; o >>= 1) {
             int ob = __shfl_xor_sync(0xffffffffu, best, o), oa = __shfl_xor_sync(0xffffffffu, arg, o);
             if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
         }
-        if (lane == 0) { s_max[c][warp] = best; s_arg[c][warp] = arg; }
-    }
-    __syncthreads();
-    int nmax = 0;
-    for (int c = 0; c < C && c < 8; ++c) {
-        int best = s_max[c][0], arg = s_arg[c][0];
-        for (int w = 1; w < 4; ++w)
-            if (s_max[c][w] > best || (s_max[c][w] == best && s_arg[c][w] < arg)) { best = s_max[c][w]; arg = s_arg[c][w]; }
         cmaxAll[c] = best;
-        amaxAll[c] = arg;
         nmax = max(nmax, arg + 500);
     }
     const int n = min(nmax, 2048);
@@ -84,32 +78,35 @@ k_transient(const short* __restrict__ pcm, const int* __restrict__ blkOff, const
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         if (c >= C) break;
-        uint4 v4;
-        if (c < 4) v4 = held[c];
-        else {
-            const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
-            short t[8];
-            for (int e = 0; e < 8; ++e) t[e] = p[tid * 8 + e];
-            v4 = *reinterpret_cast<uint4*>(t);
-        }
-        const short* q = reinterpret_cast<const short*>(&v4);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            int v = q[e];
-            if (tid * 8 + e < nn) sum += (unsigned long long)((v < 0 ? -v : v) & 0x7fff);
+        for (int j = 0; j < 4; ++j) {
+            uint4 v4;
+            if (c < 2) v4 = held[c][j];
+            else {
+                const short* p = pcm + ((long long)blkOff[s] * C + (long long)c * nbs + k) * 1024;
+                short t[8];
+                for (int e = 0; e < 8; ++e) t[e] = p[lane * 32 + j * 8 + e];
+                v4 = *reinterpret_cast<uint4*>(t);
+            }
+            const short* q = reinterpret_cast<const short*>(&v4);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                int v = q[e];
+                if (lane * 32 + j * 8 + e < nn) sum += (unsigned long long)((v < 0 ? -v : v) & 0x7fff);
+            }
         }
     }
     for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0) s_sum[warp] = sum;
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long S = s_sum[0] + s_sum[1] + s_sum[2] + s_sum[3];
+    if (lane == 0) {
         bool t = false;
-        if (S != 0)
-            for (int c = 0; c < C && c < 8; ++c)
-                if (2ull * (unsigned long long)cmaxAll[c] * (unsigned long long)(C * n) > 9ull * S) t = true;
+        if (sum != 0) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                if (c >= C) break;
+                if (2ull * (unsigned long long)cmaxAll[c] * (unsigned long long)(C * n) > 9ull * sum) t = true;
+            }
+        }
         det[g] = t ? 1 : 0;
-        (void)amaxAll; (void)s_n;
     }
 }
 
@@ -644,7 +641,7 @@ extern "C" int pac_encode_streams(pac_ctx* ctx, const short* d_pcm, const int* h
     PAC_CHECK(cudaMemsetAsync(sb + oErr, 0, sizeof(int), st));
     ctx->kevN[0] = ctx->kevN[1] = 0;
     ctx->launches += 6;       // k_transient, k_sizes, the two kernels of the cub scan, k_gather, k_headers (per batch below: k_encode, k_bitalloc, k_pvq, k_pack)
-    k_transient<<<(unsigned)totBlk, 128, 0, st>>>(d_pcm, dBlkOff, dNb, S, C, sb + oDet);
+    k_transient<<<(unsigned)((totBlk + TR_WARPS - 1) / TR_WARPS), TR_WARPS * 32, 0, st>>>(d_pcm, dBlkOff, dNb, S, C, (int)totBlk, sb + oDet);
     EncArgs a;
     a.pcm = d_pcm; a.blkOff = dBlkOff; a.nb = dNb; a.wbOff = dWbOff; a.det = sb + oDet; a.nStreams = S;
     a.rec = sb + oRec; a.recBytes = (int*)(sb + oRecB); a.zeroSub = sb + oZero; a.err = (int*)(sb + oErr);
