@@ -112,10 +112,19 @@ __device__ __forceinline__ void enf_frame(const PacDev* __restrict__ dev, const 
 
     // (1) window + MDCT (coder/codec.py:301-305)
     ENF_PH_START(N == PAC_NLONG ? 0 : 32);
+    // long frames: the first quadrant of the 1024-point roots (4 KB) goes to shared memory - in S.mk, which is free until
+    // the Hann FFT is over - and serves both FFTs (fft.cuh: tw_quarter)
+    constexpr bool QT = N == PAC_NLONG;
+    cplx<T>* qtab = reinterpret_cast<cplx<T>*>(S.mk);
+    if (QT) {
+        const cplx<T>* r1024 = reinterpret_cast<const cplx<T>*>(tabsT.tw_fft[3]);
+        for (int i = tid; i < 256; i += NT) qtab[i] = r1024[i];
+    }
     enf_fold<T, N, NT>(x, win, tw, fbuf, tid);
     __syncthreads();
     ENF_PH(0);
-    cta_fft<T, Q, 1, NT>(fbuf, rootsQ, tid);
+    if (QT) cta_fft<T, Q, 1, NT, 1>(fbuf, qtab, tid);       // 512-point: an index is worth 2 in the 1024-point table
+    else cta_fft<T, Q, 1, NT>(fbuf, rootsQ, tid);
     ENF_PH(1);
     mdct_post<T, N, 1, NT, double>(fbuf, tw, (T)2 / (T)N, S.lines, tid);
     __syncthreads();
@@ -131,7 +140,7 @@ __device__ __forceinline__ void enf_frame(const PacDev* __restrict__ dev, const 
     }
     __syncthreads();
     ENF_PH(3);
-    hann_rfft_finish<N, NT, T>(pc, fbuf, mkT, tid);
+    hann_rfft_finish<N, NT, T, QT>(pc, fbuf, mkT, tid, qtab);
     ENF_PH(4);
     if (sbr) {                                    // coder/codec.py:460-473
         double m2 = 0.0;

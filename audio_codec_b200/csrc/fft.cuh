@@ -74,8 +74,22 @@ template <typename T, int R> __device__ __forceinline__ void bfly(cplx<T>* u) {
     else bfly8(u);
 }
 
+// exp(-2 pi j m / 1024) from its first quadrant q[0..256) (the tables are built symmetric, pac_api.cu: the value is the
+// full table's entry bit for bit).  The front end keeps this quarter in shared memory: the full tables (16 KB + 8 KB,
+// strided access) do not stay in the 28 KB of L1 its six CTAs leave, and every pass waited on L2 for its twiddles.
+template <typename T> __device__ __forceinline__ cplx<T> tw_quarter(const cplx<T>* q, int m) {
+    const cplx<T> b = q[m & 255];
+    const int qd = m >> 8;                                 // times (-j)^qd
+    const T x = (qd & 1) ? b.y : b.x, y = (qd & 1) ? b.x : b.y;
+    cplx<T> r;
+    r.x = (qd == 2 || qd == 3) ? -x : x;
+    r.y = (qd == 1 || qd == 2) ? -y : y;
+    return r;
+}
+
 // One Stockham pass of radix R at sub-transform size Ns (product of earlier radices).
-template <typename T, int N, int R, int B, int NT>
+// QSH >= 0: `roots` is the quarter table of the 1024-point roots and an index of this transform is worth 1 << QSH there.
+template <typename T, int N, int R, int B, int NT, int QSH = -1>
 __device__ __forceinline__ void fft_pass(cplx<T>* buf, const cplx<T>* __restrict__ roots, int Ns, int tid) {
     constexpr int J = N / R;
     constexpr int TOT = B * J;
@@ -92,7 +106,7 @@ __device__ __forceinline__ void fft_pass(cplx<T>* buf, const cplx<T>* __restrict
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 cplx<T> v = p[r * J];
-                if (r > 0 && Ns > 1) v = cmul(v, roots[r * step]);
+                if (r > 0 && Ns > 1) v = cmul(v, QSH >= 0 ? tw_quarter<T>(roots, (r * step) << (QSH >= 0 ? QSH : 0)) : roots[r * step]);
                 u[it][r] = v;
             }
             bfly<T, R>(u[it]);
@@ -114,7 +128,7 @@ __device__ __forceinline__ void fft_pass(cplx<T>* buf, const cplx<T>* __restrict
 }
 
 // Full transform.  Radix plan: as many radix-8 passes as fit, then 4, then 2.
-template <typename T, int N, int B, int NT>
+template <typename T, int N, int B, int NT, int QSH = -1>
 __device__ __forceinline__ void cta_fft(cplx<T>* buf, const cplx<T>* __restrict__ roots, int tid) {
     int Ns = 1;
     constexpr int L2 = (N == 64) ? 6 : (N == 128) ? 7 : (N == 512) ? 9 : 10;
@@ -122,9 +136,9 @@ __device__ __forceinline__ void cta_fft(cplx<T>* buf, const cplx<T>* __restrict_
     constexpr int REM = L2 - 3 * N8;
 #pragma unroll
     for (int p = 0; p < N8; ++p) {
-        fft_pass<T, N, 8, B, NT>(buf, roots, Ns, tid);
+        fft_pass<T, N, 8, B, NT, QSH>(buf, roots, Ns, tid);
         Ns *= 8;
     }
-    if (REM == 2) fft_pass<T, N, 4, B, NT>(buf, roots, Ns, tid);
-    if (REM == 1) fft_pass<T, N, 2, B, NT>(buf, roots, Ns, tid);
+    if (REM == 2) fft_pass<T, N, 4, B, NT, QSH>(buf, roots, Ns, tid);
+    if (REM == 1) fft_pass<T, N, 2, B, NT, QSH>(buf, roots, Ns, tid);
 }

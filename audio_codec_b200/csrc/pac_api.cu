@@ -167,12 +167,29 @@ template <typename T> static int make_numeric_tables(pac_ctx* c, PacTables<T>* t
     };
     if ((rc = twid(PAC_NLONG, &t->tw_mdct_long))) return rc;
     if ((rc = twid(PAC_NSHORT, &t->tw_mdct_short))) return rc;
-    auto roots = [&](int n, int count, const T** out) {   // exp(-2 pi j k/n), k < count
+    // exp(-2 pi j k/n), k < count.  n divides 2048: every table is read off ONE first quadrant of the 2048-point roots by
+    // symmetry (times (-j)^quadrant), so that the tables agree with each other entry for entry and a kernel that keeps only
+    // a quadrant (fft.cuh: tw_quarter) reproduces them bit for bit; axis points are exact.
+    std::vector<double> qc(513), qs(513);                  // cos, sin of 2 pi i / 2048, i <= 512
+    for (int i = 0; i <= 512; ++i) {
+        qc[i] = (double)cosl(2 * pi * i / 2048);
+        qs[i] = (double)sinl(2 * pi * i / 2048);
+    }
+    qc[512] = 0.0; qs[512] = 1.0; qc[0] = 1.0; qs[0] = 0.0;
+    auto roots = [&](int n, int count, const T** out) {
         std::vector<double> v(2 * count);
         for (int k = 0; k < count; ++k) {
-            long double a = -2 * pi * k / n;
-            v[2 * k] = (double)cosl(a);
-            v[2 * k + 1] = (double)sinl(a);
+            const int m = (int)(((long long)k * (2048 / n)) % 2048), qd = m / 512, i = m % 512;
+            const double re = qc[i], im = -qs[i];          // quadrant 0
+            double x, y;
+            switch (qd) {
+                case 0: x = re; y = im; break;
+                case 1: x = im; y = -re; break;            // times -j
+                case 2: x = -re; y = -im; break;
+                default: x = -im; y = re; break;           // times +j
+            }
+            v[2 * k] = x;
+            v[2 * k + 1] = y;
         }
         return up(v, out);
     };
