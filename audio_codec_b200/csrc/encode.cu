@@ -321,7 +321,7 @@ __device__ __forceinline__ void epre_band_layout(const PacBands& bands, int f, i
 #define PQ_SORT 1
 #endif
 #ifndef PQ_MINB
-#define PQ_MINB 3          // 80 registers: the compiler takes 158 when free (half the threads per SM; measured: 53.6 -> 50.9 ms encode)
+#define PQ_MINB 4          // 64 registers, 1024 threads per SM (the compiler takes 158 when free; measured 2 / 3 / 4 / 5 CTAs of 256 threads: 9.4 / 8.1 / 7.5 / 8.4 ms)
 #endif
 __global__ void __launch_bounds__(PQ_NT, PQ_MINB)
 k_pvq(const PacDev* __restrict__ dev, EncArgs a, int nChunks, double* __restrict__ ws, int* __restrict__ yws,
